@@ -1,0 +1,416 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a -- the tensor-core core of the decoder, ViT and STC linears.
+//
+//   C[M,N] = epi( alpha * ( sum_k A1[m,k] B1[n,k]  +  sum_k A2[m,k] B2[n,k] ) )
+//   epi(v) = round_bf16( act(v + bias[n]) ) (+ residual[m,n])
+//
+// The second (A2,B2) operand pair is the fused LoRA update: with A2 = s*(x A^T) [M,R] and B2 = lora_B [N,R]
+// the rank-R product is accumulated into the SAME TMEM accumulator as the frozen base weight product, as
+// one extra 64-wide k-block after the K/64 base blocks. This replaces peft's three GEMMs + add per linear
+// (reference: src/litmodule/videollama2_vlb_litmodule.py:113-120 wraps every decoder linear in lora.Linear).
+//
+// Structure (one CTA per SM, persistent over output tiles):
+//   warp 0      : TMA producer (cp.async.bulk.tensor, 128B swizzle) -> STAGES-deep smem ring, mbarrier full/empty
+//   warp 1      : MMA issuer (single thread, tcgen05.mma cta_group::1 kind::f16, M=128, N=BN, K=16)
+//   warp 2      : TMEM allocator (2 accumulator stages x BN columns)
+//   warps 4..7  : epilogue: tcgen05.ld -> registers -> bias/act/residual -> bf16 -> swizzled smem -> TMA store
+// Operands may be K-major (row-major [rows, K]) or MN-major (row-major [K, rows]); the latter lets the
+// backward contract over N (dX = dY W) or over M (dW-like products) without materialising transposes.
+#include "common.cuh"
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <string.h>
+
+namespace vlb {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int GEMM_THREADS = 256;
+constexpr int CD_STAGE_BYTES = BM * 128;          // 128 rows x 64 bf16
+constexpr int SMEM_AB_BYTES = 192 * 1024;
+
+template <int BN> struct GemmCfg {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = SMEM_AB_BYTES / STAGE_BYTES;
+    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * CD_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct GemmParams {
+    int M, N;
+    int nk1, nk2;           // number of 64-wide k-blocks from operand pair 1 and 2
+    float alpha;
+    const bf16* bias;       // [N] or null
+    const bf16* residual;   // [M, ldr] or null
+    int ldr;
+    int act;
+    int mt, nt;             // tile counts
+};
+
+__device__ __forceinline__ void tile_coords(int t, int mt, int nt, int& mb, int& nb) {
+    constexpr int GROUP_M = 8;
+    const int per_group = GROUP_M * nt;
+    const int g = t / per_group;
+    const int first_m = g * GROUP_M;
+    const int gm = min(GROUP_M, mt - first_m);
+    const int r = t - g * per_group;
+    mb = first_m + (r % gm);
+    nb = r / gm;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const GemmParams p,
+                    const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                    const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                    const __grid_constant__ CUtensorMap tmC) {
+    using Cfg = GemmCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES * Cfg::A_BYTES;
+    uint8_t* smem_cd = smem + STAGES * Cfg::STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_cd + 2 * CD_STAGE_BYTES);
+    uint64_t* full_bar = bars;                    // [STAGES]
+    uint64_t* empty_bar = bars + STAGES;          // [STAGES]
+    uint64_t* tfull_bar = bars + 2 * STAGES;      // [2]
+    uint64_t* tempty_bar = bars + 2 * STAGES + 2; // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int nk = p.nk1 + p.nk2;
+    const int num_tiles = p.mt * p.nt;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA1); tma_prefetch_desc(&tmB1); tma_prefetch_desc(&tmC);
+        if (p.nk2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 128); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                int mb, nb; tile_coords(t, p.mt, p.nt, mb, nb);
+                const int m0 = mb * BM, n0 = nb * BN;
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                    const bool second = kb >= p.nk1;
+                    const CUtensorMap* ta = second ? &tmA2 : &tmA1;
+                    const CUtensorMap* tb = second ? &tmB2 : &tmB1;
+                    const int k0 = (second ? kb - p.nk1 : kb) * BK;
+                    uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
+                    uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
+                    if constexpr (!A_MN) {
+                        tma_load_2d(ta, &full_bar[stage], sa, k0, m0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j)
+                            tma_load_2d(ta, &full_bar[stage], sa + j * (BK * 128), m0 + j * 64, k0);
+                    }
+                    if constexpr (!B_MN) {
+                        tma_load_2d(tb, &full_bar[stage], sb, k0, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(tb, &full_bar[stage], sb + j * (BK * 128), n0 + j * 64, k0);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (one thread)
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+            // K-major: SBO = 1024 B (8 rows x 128 B), LBO unused. MN-major: SBO = 1024 B (8 k-rows), LBO = atom stride.
+            constexpr uint32_t LBO = BK * 128;
+            constexpr uint32_t KSTEP_A = A_MN ? (16 * 128) : 32;   // bytes to advance per UMMA_K=16
+            constexpr uint32_t KSTEP_B = B_MN ? (16 * 128) : 32;
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(&tempty_bar[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_BYTES);
+                    const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t ad = make_smem_desc(a_addr + k * KSTEP_A, A_MN ? LBO : 0, 1024);
+                        const uint64_t bd = make_smem_desc(b_addr + k * KSTEP_B, B_MN ? LBO : 0, 1024);
+                        umma_bf16(d_tmem, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);                 // frees this smem stage when the MMAs retire
+                    if (kb == nk - 1) umma_commit(&tfull_bar[as]);  // accumulator ready for the epilogue
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ epilogue (128 threads)
+        const int q = warp & 3;                 // TMEM lane quarter this warp may access
+        const int row = q * 32 + lane;
+        int it = 0;
+        uint32_t cd_idx = 0;
+        const bool issuer = (warp == 4 && lane == 0);
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            int mb, nb; tile_coords(t, p.mt, p.nt, mb, nb);
+            const int m0 = mb * BM, n0 = nb * BN;
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            mbar_wait(&tfull_bar[as], aphase);
+            tc_fence_after();
+            const int m = m0 + row;
+            const bool m_ok = m < p.M;
+#pragma unroll 1
+            for (int s = 0; s < BN / 64; ++s, ++cd_idx) {
+                uint8_t* cd = smem_cd + (cd_idx & 1) * CD_STAGE_BYTES;
+                if (issuer) tma_store_wait_read<1>();       // the store that last used this buffer has been read out
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t r[32];
+                    const int c0 = s * 64 + h * 32;
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+                    tmem_ld_wait();
+                    const int n = n0 + c0;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {           // 4 chunks of 8 columns (16 B of bf16)
+                        float v[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
+                        const int nn = n + c * 8;
+                        const bool n_ok = nn < p.N;         // N is a multiple of 8
+                        if (p.bias != nullptr && n_ok) {
+                            float b[8]; load8(p.bias + nn, b);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] += b[j];
+                        }
+                        if (p.act != ACT_NONE) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
+                        }
+                        if (p.residual != nullptr && m_ok && n_ok) {
+                            float rr[8]; load8(p.residual + (size_t)m * p.ldr + nn, rr);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = bf2f(f2bf(v[j])) + rr[j];
+                        }
+                        uint4 u;
+                        u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);
+                        u.z = pack_bf16(v[4], v[5]); u.w = pack_bf16(v[6], v[7]);
+                        const int chunk = h * 4 + c;        // 16-byte chunk index inside the 128-byte row
+                        *reinterpret_cast<uint4*>(cd + row * 128 + ((chunk ^ (row & 7)) << 4)) = u;
+                    }
+                }
+                if (s == BN / 64 - 1) {                     // all TMEM reads of this accumulator stage are done
+                    tc_fence_before();
+                    mbar_arrive(&tempty_bar[as]);
+                }
+                fence_proxy_async_smem();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (issuer) {
+                    tma_store_2d(&tmC, cd, n0 + s * 64, m0);
+                    tma_store_commit();
+                }
+            }
+        }
+        if (issuer) tma_store_wait_all<0>();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc<Cfg::TMEM_COLS>(tmem_base); }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+    static PFN_encodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(ptr);
+    });
+    return fn;
+}
+
+struct TmKey {
+    const void* ptr; uint64_t d0, d1, stride; uint32_t b0, b1;
+    bool operator==(const TmKey& o) const {
+        return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && stride == o.stride && b0 == o.b0 && b1 == o.b1;
+    }
+};
+struct TmHash {
+    size_t operator()(const TmKey& k) const {
+        size_t h = reinterpret_cast<size_t>(k.ptr);
+        h = h * 1000003u ^ k.d0; h = h * 1000003u ^ k.d1; h = h * 1000003u ^ k.stride;
+        h = h * 1000003u ^ k.b0; h = h * 1000003u ^ k.b1;
+        return h;
+    }
+};
+static std::mutex g_tm_mutex;
+static std::unordered_map<TmKey, CUtensorMap, TmHash> g_tm_cache;
+
+// 2-D bf16 tensor map, row-major [d1 rows, d0 cols] with row stride `stride_elems`, box [b1 rows, b0 cols], SW128.
+static int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride_elems,
+                     uint32_t b0, uint32_t b1) {
+    TmKey key{ptr, d0, d1, stride_elems, b0, b1};
+    {
+        std::lock_guard<std::mutex> lk(g_tm_mutex);
+        auto it = g_tm_cache.find(key);
+        if (it != g_tm_cache.end()) { *out = it->second; return 0; }
+    }
+    PFN_encodeTiled enc = get_encode();
+    VLB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    VLB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand %p is not 16-byte aligned", ptr);
+    VLB_REQUIRE((stride_elems * 2) % 16 == 0, "TMA row stride %llu elements is not a multiple of 16 bytes",
+                (unsigned long long)stride_elems);
+    cuuint64_t dims[2] = {d0, d1};
+    cuuint64_t strides[1] = {stride_elems * 2};
+    cuuint32_t box[2] = {b0, b1};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    VLB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) ptr=%p dims=%llu,%llu stride=%llu box=%u,%u",
+                (int)r, ptr, (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)stride_elems, b0, b1);
+    std::lock_guard<std::mutex> lk(g_tm_mutex);
+    if (g_tm_cache.size() > 65536) g_tm_cache.clear();
+    g_tm_cache.emplace(key, *out);
+    return 0;
+}
+
+void tmap_cache_clear() {
+    std::lock_guard<std::mutex> lk(g_tm_mutex);
+    g_tm_cache.clear();
+}
+
+struct GemmArgs {
+    const void* A1; int lda1; int K1;
+    const void* B1; int ldb1;
+    const void* A2; int lda2; int K2;
+    const void* B2; int ldb2;
+    void* C; int ldc;
+    int M, N;
+    float alpha;
+    const void* bias; const void* residual; int ldr; int act;
+    int a_mn, b_mn;     // operand storage: 0 = [rows, K] (K-major), 1 = [K, rows] (MN-major)
+    int max_ctas;       // 0 = all SMs
+};
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
+    using Cfg = GemmCfg<BN>;
+    CUtensorMap tA1, tB1, tA2, tB2, tC;
+    int rc;
+    if (!A_MN) rc = make_tmap(&tA1, a.A1, a.K1, a.M, a.lda1, BK, BM);
+    else       rc = make_tmap(&tA1, a.A1, a.M, a.K1, a.lda1, 64, BK);
+    if (rc) return rc;
+    if (!B_MN) rc = make_tmap(&tB1, a.B1, a.K1, a.N, a.ldb1, BK, BN);
+    else       rc = make_tmap(&tB1, a.B1, a.N, a.K1, a.ldb1, 64, BK);
+    if (rc) return rc;
+    if (a.K2 > 0) {
+        if (!A_MN) rc = make_tmap(&tA2, a.A2, a.K2, a.M, a.lda2, BK, BM);
+        else       rc = make_tmap(&tA2, a.A2, a.M, a.K2, a.lda2, 64, BK);
+        if (rc) return rc;
+        if (!B_MN) rc = make_tmap(&tB2, a.B2, a.K2, a.N, a.ldb2, BK, BN);
+        else       rc = make_tmap(&tB2, a.B2, a.N, a.K2, a.ldb2, 64, BK);
+        if (rc) return rc;
+    } else { tA2 = tA1; tB2 = tB1; }
+    rc = make_tmap(&tC, a.C, a.N, a.M, a.ldc, 64, BM);
+    if (rc) return rc;
+
+    GemmParams p;
+    p.M = a.M; p.N = a.N;
+    p.nk1 = ceil_div(a.K1, BK); p.nk2 = a.K2 > 0 ? ceil_div(a.K2, BK) : 0;
+    p.alpha = a.alpha;
+    p.bias = reinterpret_cast<const bf16*>(a.bias);
+    p.residual = reinterpret_cast<const bf16*>(a.residual);
+    p.ldr = a.ldr; p.act = a.act;
+    p.mt = ceil_div(a.M, BM); p.nt = ceil_div(a.N, BN);
+
+    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        VLB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(gemm smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+        attr_set = true;
+    }
+    int grid = p.mt * p.nt;
+    int cap = a.max_ctas > 0 ? a.max_ctas : num_sms();
+    if (grid > cap) grid = cap;
+    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC);
+    return check_launch("gemm_tcgen05_kernel");
+}
+
+template <int BN>
+static int dispatch_major(const GemmArgs& a, cudaStream_t s) {
+    if (!a.a_mn && !a.b_mn) return launch_gemm<BN, false, false>(a, s);
+    if (!a.a_mn && a.b_mn)  return launch_gemm<BN, false, true>(a, s);
+    if (a.a_mn && !a.b_mn)  return launch_gemm<BN, true, false>(a, s);
+    return launch_gemm<BN, true, true>(a, s);
+}
+
+int gemm_dispatch(const GemmArgs& a, int block_n, cudaStream_t s) {
+    VLB_REQUIRE(a.M > 0 && a.N > 0 && a.K1 > 0, "gemm: bad shape M=%d N=%d K=%d", a.M, a.N, a.K1);
+    VLB_REQUIRE(a.N % 8 == 0, "gemm: N=%d must be a multiple of 8", a.N);
+    int bn = block_n;
+    if (bn == 0) bn = (a.N >= 256 && a.N % 256 == 0) ? 256 : (a.N > 64 ? 128 : 64);
+    if (bn == 256) {
+        // prefer 128-wide tiles when 256-wide ones cannot fill the machine
+        long long tiles = (long long)ceil_div(a.M, BM) * ceil_div(a.N, 256);
+        if (block_n == 0 && tiles < num_sms()) bn = 128;
+    }
+    switch (bn) {
+        case 256: return dispatch_major<256>(a, s);
+        case 128: return dispatch_major<128>(a, s);
+        case 64:  return dispatch_major<64>(a, s);
+        default: VLB_REQUIRE(false, "gemm: unsupported block_n=%d", bn);
+    }
+    return 1;
+}
+
+}  // namespace vlb
+
+extern "C" int vlb_gemm_bf16(const void* A, int lda, const void* B, int ldb, void* C, int ldc,
+                             int M, int N, int K,
+                             const void* A2, int lda2, const void* B2, int ldb2, int K2,
+                             float alpha, const void* bias, const void* residual, int ldr, int act,
+                             int a_mn_major, int b_mn_major, int block_n, int max_ctas, void* stream) {
+    vlb::GemmArgs a;
+    a.A1 = A; a.lda1 = lda; a.K1 = K; a.B1 = B; a.ldb1 = ldb;
+    a.A2 = A2; a.lda2 = lda2; a.K2 = (A2 && B2) ? K2 : 0; a.B2 = B2; a.ldb2 = ldb2;
+    a.C = C; a.ldc = ldc; a.M = M; a.N = N; a.alpha = alpha;
+    a.bias = bias; a.residual = residual; a.ldr = ldr; a.act = act;
+    a.a_mn = a_mn_major; a.b_mn = b_mn_major; a.max_ctas = max_ctas;
+    return vlb::gemm_dispatch(a, block_n, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" void vlb_tmap_cache_clear() { vlb::tmap_cache_clear(); }
