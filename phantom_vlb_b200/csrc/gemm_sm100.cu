@@ -47,6 +47,9 @@ struct GemmParams {
     int ldr;
     int act;
     int mt, nt;             // tile counts
+    float* c_f32;           // when non-null: fp32 output [M, ldc32] written straight from registers (gradients)
+    int ldc32;
+    int accum_f32;          // c_f32 += result instead of =
 };
 
 __device__ __forceinline__ void tile_coords(int t, int mt, int nt, int& mb, int& nb) {
@@ -183,6 +186,33 @@ gemm_tcgen05_kernel(const GemmParams p,
             tc_fence_after();
             const int m = m0 + row;
             const bool m_ok = m < p.M;
+            if (p.c_f32 != nullptr) {
+                // fp32 output path (LoRA / head gradients): registers -> global, no bf16 rounding
+#pragma unroll 1
+                for (int c0 = 0; c0 < BN; c0 += 32) {
+                    uint32_t r[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+                    tmem_ld_wait();
+                    if (m_ok) {
+                        float* dst = p.c_f32 + (size_t)m * p.ldc32 + n0 + c0;
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            if (n0 + c0 + c * 4 < p.N) {      // N is a multiple of 8
+                                float4 v = make_float4(__uint_as_float(r[c * 4]) * p.alpha, __uint_as_float(r[c * 4 + 1]) * p.alpha,
+                                                       __uint_as_float(r[c * 4 + 2]) * p.alpha, __uint_as_float(r[c * 4 + 3]) * p.alpha);
+                                if (p.accum_f32) {
+                                    const float4 o = *reinterpret_cast<const float4*>(dst + c * 4);
+                                    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                                }
+                                *reinterpret_cast<float4*>(dst + c * 4) = v;
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&tempty_bar[as]);
+                continue;
+            }
 #pragma unroll 1
             for (int s = 0; s < BN / 64; ++s, ++cd_idx) {
                 uint8_t* cd = smem_cd + (cd_idx & 1) * CD_STAGE_BYTES;
@@ -318,6 +348,7 @@ struct GemmArgs {
     const void* A2; int lda2; int K2;
     const void* B2; int ldb2;
     void* C; int ldc;
+    int c_is_f32, accum;
     int M, N;
     float alpha;
     const void* bias; const void* residual; int ldr; int act;
@@ -344,8 +375,10 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
         else       rc = make_tmap(&tB2, a.B2, a.N, a.K2, a.ldb2, 64, BK);
         if (rc) return rc;
     } else { tA2 = tA1; tB2 = tB1; }
-    rc = make_tmap(&tC, a.C, a.N, a.M, a.ldc, 64, BM);
-    if (rc) return rc;
+    if (!a.c_is_f32) {
+        rc = make_tmap(&tC, a.C, a.N, a.M, a.ldc, 64, BM);
+        if (rc) return rc;
+    } else { tC = tA1; }
 
     GemmParams p;
     p.M = a.M; p.N = a.N;
@@ -355,6 +388,8 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     p.residual = reinterpret_cast<const bf16*>(a.residual);
     p.ldr = a.ldr; p.act = a.act;
     p.mt = ceil_div(a.M, BM); p.nt = ceil_div(a.N, BN);
+    p.c_f32 = a.c_is_f32 ? reinterpret_cast<float*>(a.C) : nullptr;
+    p.ldc32 = a.ldc; p.accum_f32 = a.accum;
 
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
     static bool attr_set = false;
@@ -403,11 +438,12 @@ extern "C" int vlb_gemm_bf16(const void* A, int lda, const void* B, int ldb, voi
                              int M, int N, int K,
                              const void* A2, int lda2, const void* B2, int ldb2, int K2,
                              float alpha, const void* bias, const void* residual, int ldr, int act,
-                             int a_mn_major, int b_mn_major, int block_n, int max_ctas, void* stream) {
+                             int a_mn_major, int b_mn_major, int c_is_f32, int accumulate,
+                             int block_n, int max_ctas, void* stream) {
     vlb::GemmArgs a;
     a.A1 = A; a.lda1 = lda; a.K1 = K; a.B1 = B; a.ldb1 = ldb;
     a.A2 = A2; a.lda2 = lda2; a.K2 = (A2 && B2) ? K2 : 0; a.B2 = B2; a.ldb2 = ldb2;
-    a.C = C; a.ldc = ldc; a.M = M; a.N = N; a.alpha = alpha;
+    a.C = C; a.ldc = ldc; a.c_is_f32 = c_is_f32; a.accum = accumulate; a.M = M; a.N = N; a.alpha = alpha;
     a.bias = bias; a.residual = residual; a.ldr = ldr; a.act = act;
     a.a_mn = a_mn_major; a.b_mn = b_mn_major; a.max_ctas = max_ctas;
     return vlb::gemm_dispatch(a, block_n, reinterpret_cast<cudaStream_t>(stream));

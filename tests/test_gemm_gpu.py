@@ -1,0 +1,90 @@
+"""tcgen05 GEMM vs torch fp32 matmul on bf16-rounded inputs (tolerance: bf16 output rounding, 2^-8 rel)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(a, b, a2, b2, alpha, bias, residual, act, a_mn, b_mn):
+    A = a.float().t() if a_mn else a.float()
+    B = b.float().t() if b_mn else b.float()
+    y = A @ B.t()
+    if a2 is not None:
+        A2 = a2.float().t() if a_mn else a2.float()
+        B2 = b2.float().t() if b_mn else b2.float()
+        y = y + A2 @ B2.t()
+    y = y * alpha
+    if bias is not None:
+        y = y + bias.float()
+    if act == 1:
+        y = y * torch.sigmoid(1.702 * y)
+    elif act == 2:
+        y = torch.nn.functional.gelu(y)
+    elif act == 3:
+        y = torch.nn.functional.silu(y)
+    if residual is not None:
+        y = y.bfloat16().float() + residual.float()
+    return y
+
+
+def _close(out, ref, tol=1e-2):
+    err = (out.float() - ref).abs().max().item()
+    scale = ref.abs().max().item() + 1e-6
+    assert err / scale < tol, "max err %g scale %g" % (err, scale)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K,bn", [(256, 256, 128, 0), (300, 200, 136, 0), (1024, 512, 4096, 256),
+                                      (128, 64, 64, 64), (77, 48, 1000, 0), (2048, 1024, 512, 128)])
+def test_gemm_majors(M, N, K, bn, a_mn, b_mn):
+    from phantom_vlb_b200 import ops
+    if a_mn and M % 8:
+        M = (M + 7) // 8 * 8
+    torch.manual_seed(M * 7 + N * 3 + K)
+    dev = "cuda"
+    a = torch.randn((K, M) if a_mn else (M, K), device=dev).bfloat16()
+    b = torch.randn((K, N) if b_mn else (N, K), device=dev).bfloat16()
+    out = ops.gemm(a, b, a_mn=a_mn, b_mn=b_mn, block_n=bn)
+    torch.cuda.synchronize()
+    _close(out, _ref(a, b, None, None, 1.0, None, None, 0, a_mn, b_mn))
+
+
+@pytest.mark.parametrize("act", [0, 1, 2, 3])
+def test_gemm_epilogue_lora(act):
+    from phantom_vlb_b200 import ops
+    torch.manual_seed(act)
+    M, N, K, R = 640, 384, 1024, 16
+    dev = "cuda"
+    a = torch.randn(M, K, device=dev).bfloat16()
+    b = (torch.randn(N, K, device=dev) * 0.05).bfloat16()
+    a2 = torch.randn(M, R, device=dev).bfloat16()
+    b2 = torch.randn(N, R, device=dev).bfloat16()
+    bias = torch.randn(N, device=dev).bfloat16()
+    res = torch.randn(M, N, device=dev).bfloat16()
+    out = ops.gemm(a, b, a2=a2, b2=b2, alpha=0.5, bias=bias, residual=res, act=act)
+    torch.cuda.synchronize()
+    _close(out, _ref(a, b, a2, b2, 0.5, bias, res, act, False, False))
+
+
+def test_gemm_f32_out_accumulate():
+    from phantom_vlb_b200 import ops
+    torch.manual_seed(0)
+    M, N, K = 48, 4096, 2048          # dA-like: contraction over the token axis, both operands MN-major
+    a = torch.randn(K, M, device="cuda").bfloat16()
+    b = torch.randn(K, N, device="cuda").bfloat16()
+    out = torch.ones(M, N, device="cuda", dtype=torch.float32)
+    ops.gemm(a, b, out, a_mn=True, b_mn=True, out_f32=True, accumulate=True, alpha=2.0)
+    torch.cuda.synchronize()
+    ref = 1.0 + 2.0 * (a.float().t() @ b.float())
+    _close(out, ref, 1e-4)
+
+
+def test_gemm_persistent_many_tiles():
+    from phantom_vlb_b200 import ops
+    torch.manual_seed(1)
+    M, N, K = 4096, 6144, 512
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    out = ops.gemm(a, b)
+    torch.cuda.synchronize()
+    _close(out, a.float() @ b.float().t())
