@@ -87,12 +87,13 @@ __device__ __forceinline__ float siluf_(float x) { return x * sigmoidf_(x); }
 __device__ __forceinline__ float quick_geluf_(float x) { return x * sigmoidf_(1.702f * x); }
 __device__ __forceinline__ float gelu_erff_(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
 
-enum Act { ACT_NONE = 0, ACT_QUICK_GELU = 1, ACT_GELU = 2, ACT_SILU = 3 };
+enum Act { ACT_NONE = 0, ACT_QUICK_GELU = 1, ACT_GELU = 2, ACT_SILU = 3, ACT_SIGMOID = 4 };
 __device__ __forceinline__ float apply_act(float x, int act) {
     switch (act) {
         case ACT_QUICK_GELU: return quick_geluf_(x);
         case ACT_GELU:       return gelu_erff_(x);
         case ACT_SILU:       return siluf_(x);
+        case ACT_SIGMOID:    return sigmoidf_(x);
         default:             return x;
     }
 }

@@ -1,0 +1,442 @@
+// Brain head: final RMSNorm -> LayerNorm1 -> HRF-weighted pooling over the token axis -> LayerNorm2 (-> dropout)
+// -> [readout GEMM runs on the tcgen05 kernel] -> MSE + ridge penalty, and the matching backward sweep.
+//   reference: src/utils.py:40-73 (HRFConvolveLayer einsum 'bse,bs->be', RidgeRegressionLayer),
+//              src/litmodule/videollama2_vlb_litmodule.py:245-254 (layer_norm1/2, dropout), :302 (mse_loss + l2_reg)
+// HBM-bound: every kernel reads its dominant operand exactly once with 16-byte accesses; rows whose HRF weight is 0
+// (system prompt, instruction, padding: ~60 % of the 2048 tokens) are never fetched in the forward pass.
+// Rounding points mirror bf16 autocast: LN outputs fp32 -> einsum operands bf16 -> pooled bf16 -> LN2 fp32 -> bf16.
+#include "common.cuh"
+
+namespace vlb {
+
+constexpr int HT = 128;       // threads per CTA in the row kernels
+constexpr int HV = 4;         // 8-element chunks per thread (H <= 8*HT*HV = 4096)
+
+struct RowStats { float rstd_rms, mean1, rstd1; };
+
+// loads row x, applies RMSNorm (bf16 rounding as MistralRMSNorm) -> z, then LN1 statistics over z.
+__device__ __forceinline__ RowStats row_norms(const bf16* __restrict__ xr, const bf16* __restrict__ wn, int H,
+                                              float eps_rms, float eps_ln, float (&z)[HV][8], float* red) {
+    const int nchunk = H / 8;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+            load8(xr + c * 8, z[i]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ss += z[i][j] * z[i][j];
+        }
+    }
+    RowStats st;
+    st.rstd_rms = rsqrtf(block_sum(ss, red) / (float)H + eps_rms);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+            float w[8]; load8(wn + c * 8, w);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { z[i][j] = bf2f(f2bf(w[j] * bf2f(f2bf(z[i][j] * st.rstd_rms)))); s += z[i][j]; }
+        }
+    }
+    st.mean1 = block_sum(s, red) / (float)H;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const float d = z[i][j] - st.mean1; sq += d * d; }
+        }
+    }
+    st.rstd1 = rsqrtf(block_sum(sq, red) / (float)H + eps_ln);
+    return st;
+}
+
+// grid (nch, B): CTA accumulates sum_s w[b,s] * bf16(LN1(RMSNorm(x[b,s]))) over its slice of rows -> partial[b, ch, :]
+__global__ void __launch_bounds__(HT) hrf_pool_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ wn,
+                                                          const bf16* __restrict__ g1, const bf16* __restrict__ b1,
+                                                          const float* __restrict__ wmask, float* __restrict__ partial,
+                                                          int S, int H, int rows_per, float eps_rms, float eps_ln) {
+    __shared__ float red[32];
+    const int b = blockIdx.y, ch = blockIdx.x, nch = gridDim.x;
+    const int nchunk = H / 8;
+    float acc[HV][8];
+#pragma unroll
+    for (int i = 0; i < HV; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    const int s0 = ch * rows_per, s1 = min(S, s0 + rows_per);
+    for (int s = s0; s < s1; ++s) {
+        const float wgt = wmask[(size_t)b * S + s];
+        if (wgt == 0.f) continue;                                  // uniform across the CTA
+        float z[HV][8];
+        const RowStats st = row_norms(x + ((size_t)b * S + s) * H, wn, H, eps_rms, eps_ln, z, red);
+#pragma unroll
+        for (int i = 0; i < HV; ++i) {
+            const int c = threadIdx.x + i * HT;
+            if (c < nchunk) {
+                float g[8], bb[8];
+                load8(g1 + c * 8, g); load8(b1 + c * 8, bb);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    acc[i][j] += wgt * bf2f(f2bf((z[i][j] - st.mean1) * st.rstd1 * g[j] + bb[j]));
+            }
+        }
+    }
+    float* dst = partial + ((size_t)b * nch + ch) * H;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) store8(dst + c * 8, acc[i]);
+    }
+}
+
+__device__ __forceinline__ float hash_uniform(unsigned long long seed, unsigned long long idx) {
+    unsigned long long z = seed + idx * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+// one CTA per batch row: pooled = bf16(sum of partials); hrf = bf16(dropout(LN2(pooled)))
+__global__ void __launch_bounds__(HT) hrf_pool_finalize_kernel(const float* __restrict__ partial, const bf16* __restrict__ g2,
+                                                               const bf16* __restrict__ b2, bf16* __restrict__ pooled,
+                                                               bf16* __restrict__ hrf, float* __restrict__ keep_scale,
+                                                               int nch, int H, float eps, float drop_p,
+                                                               unsigned long long seed) {
+    __shared__ float red[32];
+    const int b = blockIdx.x, nchunk = H / 8;
+    float v[HV][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+            for (int k = 0; k < nch; ++k) {
+                float t[8]; load8(partial + ((size_t)b * nch + k) * H + c * 8, t);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[i][j] += t[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { v[i][j] = bf2f(f2bf(v[i][j])); s += v[i][j]; }
+            store8(pooled + (size_t)b * H + c * 8, v[i]);
+        }
+    }
+    const float mean = block_sum(s, red) / (float)H;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const float d = v[i][j] - mean; sq += d * d; }
+        }
+    }
+    const float rstd = rsqrtf(block_sum(sq, red) / (float)H + eps);
+    const float inv_keep = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+            float g[8], bb[8], o[8], ks[8];
+            load8(g2 + c * 8, g); load8(b2 + c * 8, bb);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                ks[j] = 1.f;
+                if (drop_p > 0.f)
+                    ks[j] = hash_uniform(seed, (unsigned long long)b * H + c * 8 + j) < drop_p ? 0.f : inv_keep;
+                o[j] = ((v[i][j] - mean) * rstd * g[j] + bb[j]) * ks[j];
+            }
+            store8(hrf + (size_t)b * H + c * 8, o);
+            if (keep_scale) store8(keep_scale + (size_t)b * H + c * 8, ks);
+        }
+    }
+}
+
+// d = pred - bf16(y); acc[0] += sum d^2; dpred = bf16(2 d / n)   (F.mse_loss, reduction mean over B*P)
+__global__ void head_loss_kernel(const bf16* __restrict__ pred, const float* __restrict__ y, bf16* __restrict__ dpred,
+                                 float* __restrict__ acc, long long n) {
+    __shared__ float red[32];
+    float s = 0.f;
+    const float k = 2.f / (float)n;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float d = bf2f(pred[i]) - bf2f(f2bf(y[i]));
+        s += d * d;
+        if (dpred) dpred[i] = f2bf(k * d);
+    }
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) atomicAdd(acc, s);
+}
+
+// grad = 2*lambda*W (fp32, written or accumulated) and acc[1] += sum W^2 : one sweep over the readout weight
+__global__ void l2_prefill_kernel(const bf16* __restrict__ W, float* __restrict__ grad, float* __restrict__ acc,
+                                  long long n8, float two_lambda, int write_grad) {
+    __shared__ float red[32];
+    float s = 0.f;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+        float w[8]; load8(W + i * 8, w);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s += w[j] * w[j]; w[j] *= two_lambda; }
+        if (write_grad) store8(grad + i * 8, w);
+    }
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) atomicAdd(acc + 1, s);
+}
+
+// loss = acc[0]/n + lambda*acc[1]  -> out[0]; out[1] = mse, out[2] = l2
+__global__ void loss_finalize_kernel(const float* __restrict__ acc, float* __restrict__ out, float inv_n, float lambda) {
+    const float mse = acc[0] * inv_n, l2 = lambda * acc[1];
+    out[0] = mse + l2; out[1] = mse; out[2] = l2;
+}
+
+// dbias[p] = sum_b dpred[b, p]
+__global__ void colsum_kernel(const bf16* __restrict__ d, float* __restrict__ out, int B, long long P) {
+    for (long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x; p < P; p += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int b = 0; b < B; ++b) s += bf2f(d[(size_t)b * P + p]);
+        out[p] = s;
+    }
+}
+
+// LN2 backward on [B, H] (one CTA per row): dy fp32 (grad wrt hrf, before dropout scaling), x = pooled (bf16)
+__global__ void __launch_bounds__(HT) ln2_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ keep_scale,
+                                                     const bf16* __restrict__ pooled, const bf16* __restrict__ g2,
+                                                     float* __restrict__ dpooled, float* __restrict__ dg2,
+                                                     float* __restrict__ db2, int H, float eps) {
+    __shared__ float red[32];
+    const int b = blockIdx.x, nchunk = H / 8;
+    float v[HV][8], g[HV][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+            load8(pooled + (size_t)b * H + c * 8, v[i]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s += v[i][j];
+        }
+    }
+    const float mean = block_sum(s, red) / (float)H;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { v[i][j] -= mean; sq += v[i][j] * v[i][j]; }
+        }
+    }
+    const float rstd = rsqrtf(block_sum(sq, red) / (float)H + eps);
+    float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+            float gw[8];
+            load8(dy + (size_t)b * H + c * 8, g[i]);
+            load8(g2 + c * 8, gw);
+            if (keep_scale) {
+                float ks[8]; load8(keep_scale + (size_t)b * H + c * 8, ks);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) g[i][j] *= ks[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float xh = v[i][j] * rstd;
+                atomicAdd(dg2 + c * 8 + j, g[i][j] * xh);
+                atomicAdd(db2 + c * 8 + j, g[i][j]);
+                g[i][j] *= gw[j];
+                v[i][j] = xh;
+                m1 += g[i][j]; m2 += g[i][j] * xh;
+            }
+        }
+    }
+    m1 = block_sum(m1, red) / (float)H;
+    m2 = block_sum(m2, red) / (float)H;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        if (c < nchunk) {
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - m1 - v[i][j] * m2);
+            store8(dpooled + (size_t)b * H + c * 8, o);
+        }
+    }
+}
+
+// Backward of pooling + LN1 + final RMSNorm. grid (nch, B). For each row: dx = 0 if w == 0, else
+//   gu = w * bf16?(dpooled)   (grad wrt LN1 output), LN1 backward -> gz, RMSNorm backward -> dx (bf16).
+// dg1/db1 accumulate per CTA in registers and are flushed with one atomicAdd per element.
+__global__ void __launch_bounds__(HT) hrf_pool_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ wn,
+                                                          const bf16* __restrict__ g1, const float* __restrict__ wmask,
+                                                          const float* __restrict__ dpooled, bf16* __restrict__ dx,
+                                                          float* __restrict__ dg1, float* __restrict__ db1, int S, int H,
+                                                          int rows_per, float eps_rms, float eps_ln) {
+    __shared__ float red[32];
+    const int b = blockIdx.y, ch = blockIdx.x, nchunk = H / 8;
+    float ag[HV][8], ab[HV][8], dp[HV][8];
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { ag[i][j] = 0.f; ab[i][j] = 0.f; dp[i][j] = 0.f; }
+        if (c < nchunk) load8(dpooled + (size_t)b * H + c * 8, dp[i]);
+    }
+    const int s0 = ch * rows_per, s1 = min(S, s0 + rows_per);
+    bool any = false;
+    for (int s = s0; s < s1; ++s) {
+        const float wgt = wmask[(size_t)b * S + s];
+        bf16* dxr = dx + ((size_t)b * S + s) * H;
+        if (wgt == 0.f) {
+#pragma unroll
+            for (int i = 0; i < HV; ++i) {
+                const int c = threadIdx.x + i * HT;
+                if (c < nchunk) *reinterpret_cast<uint4*>(dxr + c * 8) = make_uint4(0, 0, 0, 0);
+            }
+            continue;
+        }
+        any = true;
+        const bf16* xr = x + ((size_t)b * S + s) * H;
+        float z[HV][8];
+        const RowStats st = row_norms(xr, wn, H, eps_rms, eps_ln, z, red);
+        // LN1 backward
+        float m1 = 0.f, m2 = 0.f;
+        float gz[HV][8];
+#pragma unroll
+        for (int i = 0; i < HV; ++i) {
+            const int c = threadIdx.x + i * HT;
+            if (c < nchunk) {
+                float gw[8]; load8(g1 + c * 8, gw);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float gu = wgt * dp[i][j];
+                    const float uh = (z[i][j] - st.mean1) * st.rstd1;
+                    ag[i][j] += gu * uh; ab[i][j] += gu;
+                    gz[i][j] = gu * gw[j];
+                    z[i][j] = uh;
+                    m1 += gz[i][j]; m2 += gz[i][j] * uh;
+                }
+            }
+        }
+        m1 = block_sum(m1, red) / (float)H;
+        m2 = block_sum(m2, red) / (float)H;
+        // RMSNorm backward: y = wn * (x * rstd); g = gz * wn; dx = rstd * (g - xh * mean(g * xh))
+        float dot = 0.f;
+        float xh[HV][8];
+#pragma unroll
+        for (int i = 0; i < HV; ++i) {
+            const int c = threadIdx.x + i * HT;
+            if (c < nchunk) {
+                float w[8];
+                load8(wn + c * 8, w);
+                load8(xr + c * 8, xh[i]);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    gz[i][j] = st.rstd1 * (gz[i][j] - m1 - z[i][j] * m2) * w[j];
+                    xh[i][j] *= st.rstd_rms;
+                    dot += gz[i][j] * xh[i][j];
+                }
+            }
+        }
+        dot = block_sum(dot, red) / (float)H;
+#pragma unroll
+        for (int i = 0; i < HV; ++i) {
+            const int c = threadIdx.x + i * HT;
+            if (c < nchunk) {
+                float o[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = st.rstd_rms * (gz[i][j] - xh[i][j] * dot);
+                store8(dxr + c * 8, o);
+            }
+        }
+    }
+    if (any) {
+#pragma unroll
+        for (int i = 0; i < HV; ++i) {
+            const int c = threadIdx.x + i * HT;
+            if (c < nchunk) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { atomicAdd(dg1 + c * 8 + j, ag[i][j]); atomicAdd(db1 + c * 8 + j, ab[i][j]); }
+            }
+        }
+    }
+}
+
+}  // namespace vlb
+
+using namespace vlb;
+
+extern "C" int vlb_hrf_pool_fwd(const void* x, const void* norm_w, const void* ln1_w, const void* ln1_b,
+                                const void* wmask_f32, void* partial_f32, int B, int S, int H, int nch, float eps_rms,
+                                float eps_ln, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && H <= 8 * HT * HV && nch > 0, "hrf_pool_fwd: H=%d nch=%d", H, nch);
+    const int rows_per = ceil_div(S, nch);
+    hrf_pool_fwd_kernel<<<dim3(nch, B), HT, 0, (cudaStream_t)stream>>>(
+        (const bf16*)x, (const bf16*)norm_w, (const bf16*)ln1_w, (const bf16*)ln1_b, (const float*)wmask_f32,
+        (float*)partial_f32, S, H, rows_per, eps_rms, eps_ln);
+    return check_launch("hrf_pool_fwd");
+}
+
+extern "C" int vlb_hrf_pool_finalize(const void* partial_f32, const void* ln2_w, const void* ln2_b, void* pooled,
+                                     void* hrf, void* keep_scale_f32, int B, int H, int nch, float eps, float drop_p,
+                                     unsigned long long seed, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && H <= 8 * HT * HV, "hrf_pool_finalize: H=%d", H);
+    hrf_pool_finalize_kernel<<<B, HT, 0, (cudaStream_t)stream>>>((const float*)partial_f32, (const bf16*)ln2_w,
+                                                                (const bf16*)ln2_b, (bf16*)pooled, (bf16*)hrf,
+                                                                (float*)keep_scale_f32, nch, H, eps, drop_p, seed);
+    return check_launch("hrf_pool_finalize");
+}
+
+extern "C" int vlb_head_loss(const void* pred, const void* y_f32, void* dpred, void* acc_f32, long long n,
+                             void* stream) {
+    int grid = (int)((n + 255) / 256); if (grid > num_sms() * 8) grid = num_sms() * 8;
+    head_loss_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)pred, (const float*)y_f32, (bf16*)dpred,
+                                                            (float*)acc_f32, n);
+    return check_launch("head_loss");
+}
+
+extern "C" int vlb_l2_prefill(const void* W, void* grad_f32, void* acc_f32, long long n, float lambda, int write_grad,
+                              void* stream) {
+    VLB_REQUIRE(n % 8 == 0, "l2_prefill: n=%lld must be a multiple of 8", n);
+    int grid = (int)((n / 8 + 255) / 256); if (grid > num_sms() * 8) grid = num_sms() * 8;
+    l2_prefill_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)W, (float*)grad_f32, (float*)acc_f32, n / 8,
+                                                             2.f * lambda, write_grad);
+    return check_launch("l2_prefill");
+}
+
+extern "C" int vlb_loss_finalize(const void* acc_f32, void* out_f32, long long n, float lambda, void* stream) {
+    loss_finalize_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((const float*)acc_f32, (float*)out_f32, 1.f / (float)n, lambda);
+    return check_launch("loss_finalize");
+}
+
+extern "C" int vlb_colsum(const void* d, void* out_f32, int B, long long P, void* stream) {
+    int grid = (int)((P + 255) / 256); if (grid > num_sms() * 8) grid = num_sms() * 8;
+    colsum_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)d, (float*)out_f32, B, P);
+    return check_launch("colsum");
+}
+
+extern "C" int vlb_ln2_bwd(const void* dy_f32, const void* keep_scale_f32, const void* pooled, const void* ln2_w,
+                           void* dpooled_f32, void* dg2_f32, void* db2_f32, int B, int H, float eps, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && H <= 8 * HT * HV, "ln2_bwd: H=%d", H);
+    ln2_bwd_kernel<<<B, HT, 0, (cudaStream_t)stream>>>((const float*)dy_f32, (const float*)keep_scale_f32,
+                                                      (const bf16*)pooled, (const bf16*)ln2_w, (float*)dpooled_f32,
+                                                      (float*)dg2_f32, (float*)db2_f32, H, eps);
+    return check_launch("ln2_bwd");
+}
+
+extern "C" int vlb_hrf_pool_bwd(const void* x, const void* norm_w, const void* ln1_w, const void* wmask_f32,
+                                const void* dpooled_f32, void* dx, void* dg1_f32, void* db1_f32, int B, int S, int H,
+                                int nch, float eps_rms, float eps_ln, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && H <= 8 * HT * HV && nch > 0, "hrf_pool_bwd: H=%d nch=%d", H, nch);
+    const int rows_per = ceil_div(S, nch);
+    hrf_pool_bwd_kernel<<<dim3(nch, B), HT, 0, (cudaStream_t)stream>>>(
+        (const bf16*)x, (const bf16*)norm_w, (const bf16*)ln1_w, (const float*)wmask_f32, (const float*)dpooled_f32,
+        (bf16*)dx, (float*)dg1_f32, (float*)db1_f32, S, H, rows_per, eps_rms, eps_ln);
+    return check_launch("hrf_pool_bwd");
+}

@@ -1,0 +1,309 @@
+// Row-wise normalisation, RoPE and SwiGLU kernels (HBM-bound; 16-byte vector accesses, warp-shuffle reductions).
+//
+// Rounding points follow the HF modules the reference reaches under bf16 weights (the oracle is the fp32 restatement):
+//   MistralRMSNorm : fp32 variance, x*rsqrt -> bf16, then * weight (bf16)     [transformers modeling_mistral.py]
+//   nn.LayerNorm   : fp32 statistics, affine in fp32, one rounding to bf16
+//   apply_rotary   : q*cos + rotate_half(q)*sin with bf16 cos/sin tables
+//   MistralMLP     : act_fn(gate) * up, act rounded to bf16 before the product
+#include "common.cuh"
+
+namespace vlb {
+
+// --------------------------------------------------------------------------------------------- RMSNorm
+// one CTA per row; H % 8 == 0; each thread walks the row in 8-element (16 B) chunks kept in registers (H <= 8*8*threads)
+template <int THREADS, int MAXV>
+__global__ void __launch_bounds__(THREADS) rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                              bf16* __restrict__ y, float* __restrict__ rstd_out,
+                                                              int H, float eps) {
+    __shared__ float red[32];
+    const size_t row = blockIdx.x;
+    const bf16* xr = x + row * H;
+    float v[MAXV][8];
+    float ss = 0.f;
+    const int nchunk = H / 8;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+            load8(xr + c * 8, v[i]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ss += v[i][j] * v[i][j];
+        }
+    }
+    ss = block_sum(ss, red);
+    const float rstd = rsqrtf(ss / (float)H + eps);
+    if (threadIdx.x == 0 && rstd_out) rstd_out[row] = rstd;
+    bf16* yr = y + row * H;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+            float wv[8], o[8];
+            load8(w + c * 8, wv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = wv[j] * bf2f(f2bf(v[i][j] * rstd));
+            store8(yr + c * 8, o);
+        }
+    }
+}
+
+// dx = dres + rstd * (g - xhat * mean(g * xhat)),  g = dy * w,  xhat = x * rstd      (w frozen: no dw)
+template <int THREADS, int MAXV>
+__global__ void __launch_bounds__(THREADS) rmsnorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                              const bf16* __restrict__ w, const float* __restrict__ rstd_in,
+                                                              const bf16* __restrict__ dres, bf16* __restrict__ dx, int H) {
+    __shared__ float red[32];
+    const size_t row = blockIdx.x;
+    const float rstd = rstd_in[row];
+    float g[MAXV][8], xh[MAXV][8];
+    float dot = 0.f;
+    const int nchunk = H / 8;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+            float wv[8];
+            load8(dy + row * H + c * 8, g[i]);
+            load8(x + row * H + c * 8, xh[i]);
+            load8(w + c * 8, wv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { g[i][j] *= wv[j]; xh[i][j] *= rstd; dot += g[i][j] * xh[i][j]; }
+        }
+    }
+    dot = block_sum(dot, red) / (float)H;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
+            if (dres) {
+                float r[8]; load8(dres + row * H + c * 8, r);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] += r[j];
+            }
+            store8(dx + row * H + c * 8, o);
+        }
+    }
+}
+
+// --------------------------------------------------------------------------------------------- LayerNorm (+residual, +act)
+// y = act( LN(x) * w + b  (+ residual) ).  Used for CLIP LN (act none) and timm LayerNorm2d on NHWC rows (+SiLU).
+template <int THREADS, int MAXV>
+__global__ void __launch_bounds__(THREADS) layernorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                                const bf16* __restrict__ b, const bf16* __restrict__ residual,
+                                                                bf16* __restrict__ y, int H, float eps, int act) {
+    __shared__ float red[32];
+    const size_t row = blockIdx.x;
+    float v[MAXV][8];
+    float s = 0.f;
+    const int nchunk = H / 8;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+            load8(x + row * H + c * 8, v[i]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s += v[i][j];
+        }
+    }
+    const float mean = block_sum(s, red) / (float)H;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const float d = v[i][j] - mean; ss += d * d; }
+        }
+    }
+    const float rstd = rsqrtf(block_sum(ss, red) / (float)H + eps);
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+            float wv[8], bv[8], o[8];
+            load8(w + c * 8, wv);
+            load8(b + c * 8, bv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * wv[j] + bv[j];
+            if (residual) {
+                float r[8]; load8(residual + row * H + c * 8, r);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = bf2f(f2bf(o[j])) + r[j];
+            }
+            if (act != ACT_NONE) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = apply_act(o[j], act);
+            }
+            store8(y + row * H + c * 8, o);
+        }
+    }
+}
+
+// --------------------------------------------------------------------------------------------- RoPE (in place on fused qkv rows)
+// qkv row layout: [Hq*D | Hkv*D | Hkv*D]; rotates the first (Hq+Hkv) heads. cos/sin: bf16 tables [S, D/2].
+// inverse=1 applies the transpose rotation (backward). One thread per (row, head, 8-element chunk of the first half).
+__global__ void rope_kernel(bf16* __restrict__ qkv, int ld, const bf16* __restrict__ cosT, const bf16* __restrict__ sinT,
+                            long long M, int S, int nheads, int D, int inverse) {
+    const int half = D / 2, cph = half / 8;
+    const long long total = M * nheads * cph;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cph);
+        const int h = (int)((i / cph) % nheads);
+        const long long row = i / ((long long)cph * nheads);
+        const int pos = (int)(row % S);
+        bf16* p = qkv + row * ld + h * D + c * 8;
+        float a[8], b[8], cs[8], sn[8], oa[8], ob[8];
+        load8(p, a); load8(p + half, b);
+        load8(cosT + (size_t)pos * half + c * 8, cs);
+        load8(sinT + (size_t)pos * half + c * 8, sn);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float s = inverse ? -sn[j] : sn[j];
+            // bf16 products, bf16 sum (matches q*cos + rotate_half(q)*sin evaluated in bf16)
+            oa[j] = bf2f(f2bf(a[j] * cs[j])) + bf2f(f2bf(-b[j] * s));
+            ob[j] = bf2f(f2bf(b[j] * cs[j])) + bf2f(f2bf(a[j] * s));
+        }
+        store8(p, oa); store8(p + half, ob);
+    }
+}
+
+// Backward variant fused with the fp32 -> bf16 conversion of attention's dq accumulator:
+// reads dq fp32 [M, Hq*D], applies the inverse rotation, writes bf16 into the dqkv row (q part).
+__global__ void rope_bwd_f32_kernel(const float* __restrict__ dq, bf16* __restrict__ dqkv, int ld,
+                                    const bf16* __restrict__ cosT, const bf16* __restrict__ sinT,
+                                    long long M, int S, int nheads, int D) {
+    const int half = D / 2, cph = half / 8;
+    const long long total = M * nheads * cph;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cph);
+        const int h = (int)((i / cph) % nheads);
+        const long long row = i / ((long long)cph * nheads);
+        const int pos = (int)(row % S);
+        const float* src = dq + row * (long long)nheads * D + h * D + c * 8;
+        float a[8], b[8], cs[8], sn[8], oa[8], ob[8];
+        load8(src, a); load8(src + half, b);
+        load8(cosT + (size_t)pos * half + c * 8, cs);
+        load8(sinT + (size_t)pos * half + c * 8, sn);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            oa[j] = a[j] * cs[j] + b[j] * sn[j];
+            ob[j] = b[j] * cs[j] - a[j] * sn[j];
+        }
+        bf16* p = dqkv + row * ld + h * D + c * 8;
+        store8(p, oa); store8(p + half, ob);
+    }
+}
+
+// --------------------------------------------------------------------------------------------- SwiGLU
+// gu: [M, 2I] = [gate | up];  act[M, I] = bf16(silu(gate)) * up
+__global__ void swiglu_fwd_kernel(const bf16* __restrict__ gu, bf16* __restrict__ act, long long M, int I) {
+    const int cpr = I / 8;
+    const long long total = M * cpr;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / cpr; const int c = (int)(i % cpr);
+        float g[8], u[8], o[8];
+        load8(gu + row * 2 * I + c * 8, g);
+        load8(gu + row * 2 * I + I + c * 8, u);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = bf2f(f2bf(g[j] / (1.f + __expf(-g[j])))) * u[j];
+        store8(act + row * I + c * 8, o);
+    }
+}
+// dgu[M, 2I] = [dact * up * silu'(gate) | dact * silu(gate)]
+__global__ void swiglu_bwd_kernel(const bf16* __restrict__ gu, const bf16* __restrict__ dact, bf16* __restrict__ dgu,
+                                  long long M, int I) {
+    const int cpr = I / 8;
+    const long long total = M * cpr;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / cpr; const int c = (int)(i % cpr);
+        float g[8], u[8], d[8], dg[8], du[8];
+        load8(gu + row * 2 * I + c * 8, g);
+        load8(gu + row * 2 * I + I + c * 8, u);
+        load8(dact + row * I + c * 8, d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float sg = 1.f / (1.f + __expf(-g[j]));
+            const float si = g[j] * sg;
+            du[j] = d[j] * si;
+            dg[j] = d[j] * u[j] * (sg * (1.f + g[j] * (1.f - sg)));
+        }
+        store8(dgu + row * 2 * I + c * 8, dg);
+        store8(dgu + row * 2 * I + I + c * 8, du);
+    }
+}
+
+static inline int ew_grid(long long total, int threads) {
+    long long b = ceil_div_ll(total, threads);
+    long long cap = (long long)num_sms() * 16;
+    return (int)(b < cap ? (b > 0 ? b : 1) : cap);
+}
+
+}  // namespace vlb
+
+using namespace vlb;
+
+#define NORM_DISPATCH(KERNEL, ...)                                                                   \
+    if (H <= 8 * 128 * 1)       KERNEL<128, 1><<<(unsigned)M, 128, 0, st>>>(__VA_ARGS__);            \
+    else if (H <= 8 * 128 * 2)  KERNEL<128, 2><<<(unsigned)M, 128, 0, st>>>(__VA_ARGS__);            \
+    else if (H <= 8 * 128 * 4)  KERNEL<128, 4><<<(unsigned)M, 128, 0, st>>>(__VA_ARGS__);            \
+    else                        KERNEL<256, 4><<<(unsigned)M, 256, 0, st>>>(__VA_ARGS__);
+
+extern "C" int vlb_rmsnorm_fwd(const void* x, const void* w, void* y, void* rstd, long long M, int H, float eps,
+                               void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && H <= 8192 && M > 0, "rmsnorm_fwd: bad shape M=%lld H=%d", M, H);
+    cudaStream_t st = (cudaStream_t)stream;
+    NORM_DISPATCH(rmsnorm_fwd_kernel, (const bf16*)x, (const bf16*)w, (bf16*)y, (float*)rstd, H, eps)
+    return check_launch("rmsnorm_fwd");
+}
+
+extern "C" int vlb_rmsnorm_bwd(const void* dy, const void* x, const void* w, const void* rstd, const void* dres,
+                               void* dx, long long M, int H, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && H <= 8192 && M > 0, "rmsnorm_bwd: bad shape M=%lld H=%d", M, H);
+    cudaStream_t st = (cudaStream_t)stream;
+    NORM_DISPATCH(rmsnorm_bwd_kernel, (const bf16*)dy, (const bf16*)x, (const bf16*)w, (const float*)rstd,
+                  (const bf16*)dres, (bf16*)dx, H)
+    return check_launch("rmsnorm_bwd");
+}
+
+extern "C" int vlb_layernorm_fwd(const void* x, const void* w, const void* b, const void* residual, void* y,
+                                 long long M, int H, float eps, int act, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && H <= 8192 && M > 0, "layernorm_fwd: bad shape M=%lld H=%d", M, H);
+    cudaStream_t st = (cudaStream_t)stream;
+    NORM_DISPATCH(layernorm_fwd_kernel, (const bf16*)x, (const bf16*)w, (const bf16*)b, (const bf16*)residual,
+                  (bf16*)y, H, eps, act)
+    return check_launch("layernorm_fwd");
+}
+
+extern "C" int vlb_rope(void* qkv, int ld, const void* cos_tab, const void* sin_tab, long long M, int S, int nheads,
+                        int D, int inverse, void* stream) {
+    VLB_REQUIRE(D % 16 == 0 && ld % 8 == 0, "rope: D=%d ld=%d", D, ld);
+    const long long total = M * nheads * (D / 16);
+    rope_kernel<<<ew_grid(total, 256), 256, 0, (cudaStream_t)stream>>>((bf16*)qkv, ld, (const bf16*)cos_tab,
+                                                                      (const bf16*)sin_tab, M, S, nheads, D, inverse);
+    return check_launch("rope");
+}
+
+extern "C" int vlb_rope_bwd_f32(const void* dq_f32, void* dqkv, int ld, const void* cos_tab, const void* sin_tab,
+                                long long M, int S, int nheads, int D, void* stream) {
+    VLB_REQUIRE(D % 16 == 0 && ld % 8 == 0, "rope_bwd_f32: D=%d ld=%d", D, ld);
+    const long long total = M * nheads * (D / 16);
+    rope_bwd_f32_kernel<<<ew_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        (const float*)dq_f32, (bf16*)dqkv, ld, (const bf16*)cos_tab, (const bf16*)sin_tab, M, S, nheads, D);
+    return check_launch("rope_bwd_f32");
+}
+
+extern "C" int vlb_swiglu_fwd(const void* gu, void* act, long long M, int I, void* stream) {
+    VLB_REQUIRE(I % 8 == 0, "swiglu: I=%d", I);
+    swiglu_fwd_kernel<<<ew_grid(M * (I / 8), 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)gu, (bf16*)act, M, I);
+    return check_launch("swiglu_fwd");
+}
+
+extern "C" int vlb_swiglu_bwd(const void* gu, const void* dact, void* dgu, long long M, int I, void* stream) {
+    VLB_REQUIRE(I % 8 == 0, "swiglu: I=%d", I);
+    swiglu_bwd_kernel<<<ew_grid(M * (I / 8), 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)gu, (const bf16*)dact,
+                                                                                  (bf16*)dgu, M, I);
+    return check_launch("swiglu_bwd");
+}
