@@ -36,6 +36,70 @@ int vlb_gemm_bf16(const void* A, int lda, const void* B, int ldb, void* C, int l
                   int a_mn_major, int b_mn_major, int c_is_f32, int accumulate,
                   int block_n, int max_ctas, void* stream);
 
+/* ------------------------------------------------------------------ flash attention (tcgen05, TMEM-resident S/O)
+ * q/k/v point into a fused projection buffer with row stride ld_qkv: q [B*S, Hq*D], k/v [B*S, Hkv*D].
+ * o [B*S, Hq*D] (row stride ld_o); lse [B, Hq, S] fp32 in the log2 domain (nullable for inference).
+ * Replaces flash-attn 2 selected by `_attn_implementation="flash_attention_2"`
+ * (src/litmodule/videollama2_vlb_litmodule.py:71-72; VideoLLaMA2/videollama2/model/encoder.py:24). */
+int vlb_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, void* lse_f32,
+                 int B, int S, int Hq, int Hkv, int D, int causal, float scale, void* stream);
+
+/* ------------------------------------------------------------------ norms / RoPE / SwiGLU (HBM-bound row kernels)
+ * Replace MistralRMSNorm, nn.LayerNorm / timm LayerNorm2d (NHWC rows), apply_rotary_pos_emb and MistralMLP's
+ * act_fn(gate)*up reached from VideoLLaMA2/videollama2/model/videollama2_mistral.py:94-104, encoder.py:50,
+ * projector.py:153-184. */
+int vlb_rmsnorm_fwd(const void* x, const void* w, void* y, void* rstd, long long M, int H, float eps, void* stream);
+int vlb_rmsnorm_bwd(const void* dy, const void* x, const void* w, const void* rstd, const void* dres,
+                    void* dx, long long M, int H, void* stream);
+int vlb_layernorm_fwd(const void* x, const void* w, const void* b, const void* residual, void* y,
+                      long long M, int H, float eps, int act, void* stream);
+int vlb_rope(void* qkv, int ld, const void* cos_tab, const void* sin_tab, long long M, int S, int nheads,
+             int D, int inverse, void* stream);
+int vlb_rope_bwd_f32(const void* dq_f32, void* dqkv, int ld, const void* cos_tab, const void* sin_tab,
+                     long long M, int S, int nheads, int D, void* stream);
+int vlb_swiglu_fwd(const void* gu, void* act, long long M, int I, void* stream);
+int vlb_swiglu_bwd(const void* gu, const void* dact, void* dgu, long long M, int I, void* stream);
+
+/* ------------------------------------------------------------------ vision tower / STC connector / splice gathers
+ * CLIPVisionEmbeddings + pre_layrnorm (HF, via encoder.py:50), feature_select (encoder.py:31-39), timm RegStage
+ * depthwise conv + SE (projector.py:153-184), Conv3d sampler gather (projector.py:164-174), the <video> splice of
+ * prepare_inputs_labels_for_multimodal (videollama2_arch.py:161-263), batch["language"].long()
+ * (src/litmodule/videollama2_vlb_litmodule.py:269) and make_weight_mask (litmodule.py:178-203). */
+int vlb_patch_im2col(const void* pixels_f32, void* cols, long long N, int img, int patch, int kpad, void* stream);
+int vlb_clip_embed(const void* patch, const void* cls, const void* pos, const void* lnw, const void* lnb,
+                   void* out, long long N, int T, int H, float eps, void* stream);
+int vlb_drop_cls(const void* in, void* out, long long N, int T, int H, void* stream);
+int vlb_dwconv3x3(const void* x, const void* w9c, void* y, long long F, int Hh, int Ww, int C, void* stream);
+int vlb_se_pool(const void* x, void* out, long long F, int HW, int C, void* stream);
+int vlb_se_scale(const void* x, const void* gate, void* y, long long F, int HW, int C, void* stream);
+int vlb_conv3d_gather(const void* x, void* cols, long long B, int T, int Hh, int Ww, int C, void* stream);
+int vlb_splice_embed(const void* ids_i64, const void* table, const void* vis, void* out, void* video_pos_i32,
+                     long long B, int L, int Nv, int H, int vocab, long long video_id, void* stream);
+int vlb_ids_to_long(const void* ids_f32, void* ids_i64, long long n, void* stream);
+int vlb_weight_mask(const void* padvals_i64, const void* vis_w_f64, const void* lang_w_f64, void* out_f32,
+                    int B, int Tp, int tok_per_frame, int NL, int S, void* stream);
+
+/* ------------------------------------------------------------------ brain head (pooling, readout loss, backward)
+ * layer_norm1 -> HRFConvolveLayer einsum('bse,bs->be') -> layer_norm2 -> dropout (src/utils.py:40-56,
+ * src/litmodule/videollama2_vlb_litmodule.py:245-251), F.mse_loss + l2_lambda*||W||^2 (src/utils.py:66-71,
+ * litmodule.py:302) and their backward. The readout GEMMs themselves run on vlb_gemm_bf16. */
+int vlb_hrf_pool_fwd(const void* x, const void* norm_w, const void* ln1_w, const void* ln1_b,
+                     const void* wmask_f32, void* partial_f32, int B, int S, int H, int nch, float eps_rms,
+                     float eps_ln, void* stream);
+int vlb_hrf_pool_finalize(const void* partial_f32, const void* ln2_w, const void* ln2_b, void* pooled,
+                          void* hrf, void* keep_scale_f32, int B, int H, int nch, float eps, float drop_p,
+                          unsigned long long seed, void* stream);
+int vlb_head_loss(const void* pred, const void* y_f32, void* dpred, void* acc_f32, long long n, void* stream);
+int vlb_l2_prefill(const void* W, void* grad_f32, void* acc_f32, long long n, float lambda, int write_grad,
+                   void* stream);
+int vlb_loss_finalize(const void* acc_f32, void* out_f32, long long n, float lambda, void* stream);
+int vlb_colsum(const void* d, void* out_f32, int B, long long P, void* stream);
+int vlb_ln2_bwd(const void* dy_f32, const void* keep_scale_f32, const void* pooled, const void* ln2_w,
+                void* dpooled_f32, void* dg2_f32, void* db2_f32, int B, int H, float eps, void* stream);
+int vlb_hrf_pool_bwd(const void* x, const void* norm_w, const void* ln1_w, const void* wmask_f32,
+                     const void* dpooled_f32, void* dx, void* dg1_f32, void* db1_f32, int B, int S, int H,
+                     int nch, float eps_rms, float eps_ln, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

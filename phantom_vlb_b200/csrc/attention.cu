@@ -1,0 +1,300 @@
+// Flash-style attention on tcgen05 / TMEM for sm_100a: causal GQA (Mistral decoder, d=128) and non-causal MHA
+// (CLIP ViT, d=64).  Replaces flash-attn 2 reached through `_attn_implementation="flash_attention_2"`
+// (src/litmodule/videollama2_vlb_litmodule.py:71-72, VideoLLaMA2/videollama2/model/encoder.py:24).
+//
+// Forward, one CTA per (128 query rows, head, batch element), two CTAs resident per SM:
+//   warp 0 : TMA producer   Q tile once; K/V tiles of 64 keys through 2-stage rings (3-D tensor maps [cols, S, B],
+//            so a tile never straddles two sequences and rows past S arrive as zeros)
+//   warp 1 : MMA issuer     S = Q K^T (M128 N64 K=d) into TMEM;  O += P V (M128 N=d K64) with P from shared memory
+//   warp 2 : TMEM allocator
+//   warps 4-7 : softmax     tcgen05.ld gives each thread ONE FULL ROW of S (no shuffles): scale, mask, running max
+//            with lazy rescale of the TMEM-resident O (only when the max grows by > 2^8), exp2, row sum,
+//            P -> bf16 -> 128B-swizzled shared memory; final O/l -> bf16 -> shared -> TMA store; LSE (log2 domain).
+// Right-padded text (attention_mask = ids.ne(0)) needs no extra mask under causality: valid rows never see padded
+// keys, and padded rows carry zero HRF weight so their values are don't-care.
+#include "common.cuh"
+
+namespace vlb {
+
+constexpr int ATT_BM = 128;   // query rows per CTA
+constexpr int ATT_BN = 64;    // keys per inner block
+constexpr int ATT_THREADS = 256;
+
+template <int D> struct AttCfg {
+    static constexpr int Q_BYTES = ATT_BM * D * 2;
+    static constexpr int KV_BYTES = ATT_BN * D * 2;
+    static constexpr int P_BYTES = ATT_BM * ATT_BN * 2;
+    static constexpr int OFF_K = Q_BYTES;
+    static constexpr int OFF_V = OFF_K + 2 * KV_BYTES;
+    static constexpr int OFF_P = OFF_V + 2 * KV_BYTES;
+    static constexpr int OFF_BAR = OFF_P + P_BYTES;
+    static constexpr int SMEM_BYTES = OFF_BAR + 128;          // + barriers; two CTAs fit one SM
+    static constexpr int TMEM_COLS = (ATT_BN + D <= 128) ? 128 : 256;
+    static constexpr int O_COL = ATT_BN;                      // S at column 0, O after it
+};
+
+struct AttParams {
+    int S;              // sequence length (rows per batch element)
+    int kv_len;         // keys that exist (== S)
+    int group;          // q heads per kv head
+    float scale_log2;   // softmax scale * log2(e)
+    float* lse;         // [B, Hq, S] log2-domain logsumexp
+    int Hq;
+};
+
+template <int D, bool CAUSAL>
+__global__ void __launch_bounds__(ATT_THREADS, 2)
+attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO) {
+    using Cfg = AttCfg<D>;
+    extern __shared__ __align__(1024) uint8_t smem[];      // 128B swizzle atoms need 1024-byte alignment
+    if ((smem_u32(smem) & 1023u) != 0) __trap();
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + Cfg::OFF_K;
+    uint8_t* sV = smem + Cfg::OFF_V;
+    uint8_t* sP = smem + Cfg::OFF_P;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+    uint64_t* q_full = bars;            // [1]
+    uint64_t* k_full = bars + 1;        // [2]
+    uint64_t* k_empty = bars + 3;       // [2]
+    uint64_t* v_full = bars + 5;        // [2]
+    uint64_t* v_empty = bars + 7;       // [2]
+    uint64_t* s_full = bars + 9;        // [1]
+    uint64_t* p_ready = bars + 10;      // [1] count 128
+    uint64_t* pv_done = bars + 11;      // [1]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nqb = gridDim.x;
+    const int qb = CAUSAL ? (nqb - 1 - (int)blockIdx.x) : (int)blockIdx.x;   // heavy (late) causal blocks first
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int hk = h / p.group;
+    const int q0 = qb * ATT_BM;
+    const int kv_end = CAUSAL ? min(p.kv_len, q0 + ATT_BM) : p.kv_len;
+    const int nblk = (kv_end + ATT_BN - 1) / ATT_BN;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(q_full, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+        mbar_init(s_full, 1); mbar_init(p_ready, 128); mbar_init(pv_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(q_full, Cfg::Q_BYTES);
+#pragma unroll
+            for (int c = 0; c < D / 64; ++c) tma_load_3d(&tmQ, q_full, sQ + c * (ATT_BM * 128), h * D + c * 64, q0, b);
+            for (int j = 0; j < nblk; ++j) {
+                const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
+                mbar_wait(&k_empty[st], ph ^ 1);
+                mbar_expect_tx(&k_full[st], Cfg::KV_BYTES);
+#pragma unroll
+                for (int c = 0; c < D / 64; ++c)
+                    tma_load_3d(&tmK, &k_full[st], sK + st * Cfg::KV_BYTES + c * (ATT_BN * 128), hk * D + c * 64, j * ATT_BN, b);
+                mbar_wait(&v_empty[st], ph ^ 1);
+                mbar_expect_tx(&v_full[st], Cfg::KV_BYTES);
+#pragma unroll
+                for (int c = 0; c < D / 64; ++c)
+                    tma_load_3d(&tmV, &v_full[st], sV + st * Cfg::KV_BYTES + c * (ATT_BN * 128), hk * D + c * 64, j * ATT_BN, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, false, false);
+            constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, D, false, true);
+            const uint32_t tS = tmem_base, tO = tmem_base + Cfg::O_COL;
+            auto issue_qk = [&](int j) {
+                const int st = j & 1;
+                mbar_wait(&k_full[st], (j >> 1) & 1);
+                tc_fence_after();
+                const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * Cfg::KV_BYTES);
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k) {
+                    const uint32_t off_q = (k >> 2) * (ATT_BM * 128) + (k & 3) * 32;
+                    const uint32_t off_k = (k >> 2) * (ATT_BN * 128) + (k & 3) * 32;
+                    umma_bf16(tS, make_smem_desc(qa + off_q, 0, 1024), make_smem_desc(ka + off_k, 0, 1024), idesc_qk,
+                              k > 0 ? 1u : 0u);
+                }
+                umma_commit(&k_empty[st]);
+                umma_commit(s_full);
+            };
+            mbar_wait(q_full, 0);
+            issue_qk(0);
+            for (int j = 0; j < nblk; ++j) {
+                const int st = j & 1;
+                mbar_wait(p_ready, j & 1);
+                tc_fence_after();
+                if (j + 1 < nblk) issue_qk(j + 1);
+                mbar_wait(&v_full[st], (j >> 1) & 1);
+                tc_fence_after();
+                const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * Cfg::KV_BYTES);
+#pragma unroll
+                for (int k = 0; k < ATT_BN / 16; ++k) {
+                    // A = P [128 x 64] K-major; B = V tile [64 keys x D] stored key-major rows -> MN-major operand
+                    umma_bf16(tO, make_smem_desc(pa + k * 32, 0, 1024),
+                              make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&v_empty[st]);
+                umma_commit(pv_done);
+            }
+        }
+    } else if (warp >= 4) {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        const uint32_t tS = tmem_base + lane_off, tO = tmem_base + lane_off + Cfg::O_COL;
+        const int qrow = q0 + row;
+        float m_used = -INFINITY, l = 0.f;
+        for (int j = 0; j < nblk; ++j) {
+            mbar_wait(s_full, j & 1);
+            tc_fence_after();
+            uint32_t r0[32], r1[32];
+            tmem_ld32(tS, r0);
+            tmem_ld32(tS + 32, r1);
+            tmem_ld_wait();
+            float s[64];
+#pragma unroll
+            for (int c = 0; c < 32; ++c) { s[c] = __uint_as_float(r0[c]) * p.scale_log2; s[32 + c] = __uint_as_float(r1[c]) * p.scale_log2; }
+            const int k0 = j * ATT_BN;
+            const bool need_mask = (CAUSAL && k0 + ATT_BN - 1 > q0) || (k0 + ATT_BN > p.kv_len);
+            if (need_mask) {
+                const int lim = CAUSAL ? min(qrow, p.kv_len - 1) : (p.kv_len - 1);
+#pragma unroll
+                for (int c = 0; c < 64; ++c) if (k0 + c > lim) s[c] = -INFINITY;
+            }
+            float mx = s[0];
+#pragma unroll
+            for (int c = 1; c < 64; ++c) mx = fmaxf(mx, s[c]);
+            if (j > 0) mbar_wait(pv_done, (j - 1) & 1);      // P buffer free again, O accumulator stable
+            const bool grow = mx > m_used + 8.f;
+            if (j == 0) {
+                m_used = (mx == -INFINITY) ? 0.f : mx;
+            } else if (__any_sync(0xffffffffu, grow)) {
+                tc_fence_after();
+                const float m_new = grow ? mx : m_used;
+                const float f = exp2f(m_used - m_new);
+#pragma unroll 1
+                for (int c0 = 0; c0 < D; c0 += 32) {
+                    uint32_t o[32];
+                    tmem_ld32(tO + c0, o);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * f);
+                    tmem_st32(tO + c0, o);
+                }
+                tmem_st_wait();
+                l *= f;
+                m_used = m_new;
+            }
+            float sum = 0.f;
+#pragma unroll
+            for (int c8 = 0; c8 < 8; ++c8) {
+                float e[8];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) { e[t] = exp2f(s[c8 * 8 + t] - m_used); }
+                uint4 u;
+                u.x = pack_bf16(e[0], e[1]); u.y = pack_bf16(e[2], e[3]); u.z = pack_bf16(e[4], e[5]); u.w = pack_bf16(e[6], e[7]);
+                // accumulate the row sum from the bf16-rounded probabilities actually fed to the PV MMA
+                float2 a0 = unpack_bf16(u.x), a1 = unpack_bf16(u.y), a2 = unpack_bf16(u.z), a3 = unpack_bf16(u.w);
+                sum += (a0.x + a0.y) + (a1.x + a1.y) + (a2.x + a2.y) + (a3.x + a3.y);
+                *reinterpret_cast<uint4*>(sP + row * 128 + ((c8 ^ (row & 7)) << 4)) = u;
+            }
+            l += sum;
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(p_ready);
+        }
+        // ---- epilogue: O / l -> bf16 -> smem (Q region, free: every QK MMA has retired) -> TMA store
+        mbar_wait(pv_done, (nblk - 1) & 1);
+        tc_fence_after();
+        const float inv_l = l > 0.f ? 1.f / l : 0.f;
+#pragma unroll 1
+        for (int c0 = 0; c0 < D; c0 += 32) {
+            uint32_t o[32];
+            tmem_ld32(tO + c0, o);
+            tmem_ld_wait();
+            uint8_t* dst = sQ + (c0 / 64) * (ATT_BM * 128) + row * 128;
+#pragma unroll
+            for (int c8 = 0; c8 < 4; ++c8) {
+                uint4 u;
+                u.x = pack_bf16(__uint_as_float(o[c8 * 8 + 0]) * inv_l, __uint_as_float(o[c8 * 8 + 1]) * inv_l);
+                u.y = pack_bf16(__uint_as_float(o[c8 * 8 + 2]) * inv_l, __uint_as_float(o[c8 * 8 + 3]) * inv_l);
+                u.z = pack_bf16(__uint_as_float(o[c8 * 8 + 4]) * inv_l, __uint_as_float(o[c8 * 8 + 5]) * inv_l);
+                u.w = pack_bf16(__uint_as_float(o[c8 * 8 + 6]) * inv_l, __uint_as_float(o[c8 * 8 + 7]) * inv_l);
+                const int chunk = ((c0 & 63) >> 3) + c8;
+                *reinterpret_cast<uint4*>(dst + ((chunk ^ (row & 7)) << 4)) = u;
+            }
+        }
+        if (p.lse != nullptr && qrow < p.S)
+            p.lse[((size_t)b * p.Hq + h) * p.S + qrow] = (l > 0.f) ? (m_used + log2f(l)) : -INFINITY;
+        tc_fence_before();
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == 4 && lane == 0) {
+#pragma unroll
+            for (int c = 0; c < D / 64; ++c) tma_store_3d(&tmO, sQ + c * (ATT_BM * 128), h * D + c * 64, q0, b);
+            tma_store_commit();
+            tma_store_wait_all<0>();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc<Cfg::TMEM_COLS>(tmem_base); }
+}
+
+// 3-D map over a [B, S, cols] bf16 view with row stride ld: dims (cols, S, B), box (64, rows, 1)
+static int att_tmap(CUtensorMap* m, const void* ptr, int cols, int S, int B, int ld, int box_rows) {
+    unsigned long long dims[3] = {(unsigned long long)cols, (unsigned long long)S, (unsigned long long)B};
+    unsigned long long strides[2] = {(unsigned long long)ld * 2ull, (unsigned long long)S * ld * 2ull};
+    unsigned int box[3] = {64u, (unsigned int)box_rows, 1u};
+    return encode_tmap_bf16(m, ptr, 3, dims, strides, box);
+}
+
+template <int D, bool CAUSAL>
+static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, float* lse, int B,
+                           int S, int Hq, int Hkv, float scale, cudaStream_t st) {
+    using Cfg = AttCfg<D>;
+    CUtensorMap tq, tk, tv, to;
+    int rc;
+    if ((rc = att_tmap(&tq, q, Hq * D, S, B, ld_qkv, ATT_BM))) return rc;
+    if ((rc = att_tmap(&tk, k, Hkv * D, S, B, ld_qkv, ATT_BN))) return rc;
+    if ((rc = att_tmap(&tv, v, Hkv * D, S, B, ld_qkv, ATT_BN))) return rc;
+    if ((rc = att_tmap(&to, o, Hq * D, S, B, ld_o, ATT_BM))) return rc;
+    AttParams p;
+    p.S = S; p.kv_len = S; p.group = Hq / Hkv; p.scale_log2 = scale * 1.4426950408889634f; p.lse = lse; p.Hq = Hq;
+    auto kern = attn_fwd_kernel<D, CAUSAL>;
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        VLB_REQUIRE(e == cudaSuccess, "attn_fwd smem attr (%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+        attr = true;
+    }
+    dim3 grid(ceil_div(S, ATT_BM), Hq, B);
+    kern<<<grid, ATT_THREADS, Cfg::SMEM_BYTES, st>>>(p, tq, tk, tv, to);
+    return check_launch("attn_fwd_kernel");
+}
+
+}  // namespace vlb
+
+using namespace vlb;
+
+extern "C" int vlb_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, void* lse_f32,
+                            int B, int S, int Hq, int Hkv, int D, int causal, float scale, void* stream) {
+    VLB_REQUIRE(Hkv > 0 && Hq % Hkv == 0 && (D == 64 || D == 128), "attn_fwd: Hq=%d Hkv=%d D=%d", Hq, Hkv, D);
+    VLB_REQUIRE(ld_qkv % 8 == 0 && ld_o % 8 == 0, "attn_fwd: leading dims must be multiples of 8");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (D == 128 && causal) return launch_attn_fwd<128, true>(q, k, v, ld_qkv, o, ld_o, (float*)lse_f32, B, S, Hq, Hkv, scale, st);
+    if (D == 128) return launch_attn_fwd<128, false>(q, k, v, ld_qkv, o, ld_o, (float*)lse_f32, B, S, Hq, Hkv, scale, st);
+    if (causal) return launch_attn_fwd<64, true>(q, k, v, ld_qkv, o, ld_o, (float*)lse_f32, B, S, Hq, Hkv, scale, st);
+    return launch_attn_fwd<64, false>(q, k, v, ld_qkv, o, ld_o, (float*)lse_f32, B, S, Hq, Hkv, scale, st);
+}

@@ -45,3 +45,19 @@ def gemm(a, b, out=None, *, a2=None, b2=None, alpha=1.0, bias=None, residual=Non
             float(alpha), _l.ptr(bias), _l.ptr(residual), residual.stride(0) if residual is not None else 0, int(act),
             int(a_mn), int(b_mn), int(out_f32), int(accumulate), int(block_n), int(max_ctas), _l.cur_stream())
     return out
+
+
+def attn_fwd(qkv, B, S, Hq, Hkv, D, causal, scale=None, out=None, need_lse=True):
+    """Flash attention over a fused projection buffer qkv [B*S, (Hq+2*Hkv)*D] -> (o [B*S, Hq*D], lse [B,Hq,S])."""
+    _chk(qkv, torch.bfloat16)
+    assert qkv.shape[0] == B * S and qkv.shape[1] == (Hq + 2 * Hkv) * D
+    if out is None:
+        out = torch.empty((B * S, Hq * D), device=qkv.device, dtype=torch.bfloat16)
+    lse = torch.empty((B, Hq, S), device=qkv.device, dtype=torch.float32) if need_lse else None
+    if scale is None:
+        scale = D ** -0.5
+    es = qkv.element_size()
+    base = qkv.data_ptr()
+    _l.call("vlb_attn_fwd", base, base + Hq * D * es, base + (Hq + Hkv) * D * es, qkv.stride(0), _l.ptr(out),
+            out.stride(0), _l.ptr(lse), B, S, Hq, Hkv, D, int(causal), float(scale), _l.cur_stream())
+    return out, lse
