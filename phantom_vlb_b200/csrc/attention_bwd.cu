@@ -1,0 +1,335 @@
+// Flash attention backward on tcgen05 / TMEM (causal GQA, d = 128) -- the decoder's attention gradient.
+// Replaces flash-attn 2's backward reached by autograd through `_attn_implementation="flash_attention_2"`
+// (src/litmodule/videollama2_vlb_litmodule.py:71-72).
+//
+// One CTA per (128-key block j, kv head, batch element); it keeps K_j, V_j in shared memory and dK_j, dV_j in TMEM
+// while it sweeps every query head of the GQA group and every 64-row query block i that can see the keys.
+// All score-shaped tiles are computed TRANSPOSED (keys on the 128 TMEM lanes, queries on 64 columns) so that each
+// softmax thread owns one key row, P^T / dS^T land in shared memory already in the K-major layout the dV / dK MMAs
+// want, and LSE / Delta are per-column broadcasts:
+//   (1) S^T  = K_j Q_i^T          (2) dP^T = V_j dO_i^T           [M128 N64 K128]  -> TMEM
+//   threads : P^T = exp2(S^T*c - LSE), dS^T = P^T o (dP^T - Delta)  -> bf16 -> swizzled smem
+//   (3) dV_j += P^T dO_i          (4) dK_j += dS^T Q_i            [M128 N128 K64]  accumulate in TMEM over the sweep
+//   (5) dQ_i^T = K_j^T dS^T       [M128(d) N64(q) K128(keys)]  -> TMEM -> fp32 red.global (coalesced along d)
+// warp 0 TMA producer (Q_i, dO_i, LSE_i, Delta_i through a 2-stage ring), warp 1 MMA issuer, warp 2 TMEM allocator,
+// warps 4-7 softmax / dQ reduction / epilogue.
+#include "common.cuh"
+
+namespace vlb {
+
+constexpr int BW_D = 128;
+constexpr int BW_BK = 128;      // keys per CTA
+constexpr int BW_BQ = 64;       // query rows per inner step
+constexpr int BW_THREADS = 256;
+
+struct BwCfg {
+    static constexpr int KV_BYTES = BW_BK * BW_D * 2;          // 32 KB each
+    static constexpr int QDO_BYTES = BW_BQ * BW_D * 2;         // 16 KB each
+    static constexpr int PS_BYTES = BW_BK * BW_BQ * 2;         // 16 KB each
+    static constexpr int OFF_K = 0;
+    static constexpr int OFF_V = KV_BYTES;
+    static constexpr int OFF_Q = 2 * KV_BYTES;                 // [2 stages]
+    static constexpr int OFF_DO = OFF_Q + 2 * QDO_BYTES;       // [2 stages]
+    static constexpr int OFF_P = OFF_DO + 2 * QDO_BYTES;
+    static constexpr int OFF_DS = OFF_P + PS_BYTES;
+    static constexpr int OFF_VEC = OFF_DS + PS_BYTES;          // [2 stages][lse 64 | delta 64] floats
+    static constexpr int OFF_BAR = OFF_VEC + 2 * 2 * BW_BQ * 4;
+    static constexpr int SMEM_BYTES = OFF_BAR + 128;
+    static constexpr int T_S = 0, T_DP = 64, T_DQ = 128, T_DV = 192, T_DK = 320;   // TMEM columns
+    static constexpr int TMEM_COLS = 512;
+};
+
+struct BwParams {
+    int S, Hq, Hkv, group, causal;
+    float scale, scale_log2;
+    const float* lse;       // [B, Hq, S] log2 domain
+    const float* delta;     // [B, Hq, S]
+    float* dq;              // [B*S, Hq*D] fp32, pre-zeroed
+    bf16* dk; bf16* dv;     // rows [B*S], row stride ld_dkv, head hk at column hk*D
+    int ld_dkv;
+};
+
+__global__ void __launch_bounds__(BW_THREADS, 1)
+attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO) {
+    using Cfg = BwCfg;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if ((smem_u32(smem) & 1023u) != 0) __trap();
+    uint8_t* sK = smem + Cfg::OFF_K;
+    uint8_t* sV = smem + Cfg::OFF_V;
+    uint8_t* sQ = smem + Cfg::OFF_Q;
+    uint8_t* sDO = smem + Cfg::OFF_DO;
+    uint8_t* sP = smem + Cfg::OFF_P;
+    uint8_t* sDS = smem + Cfg::OFF_DS;
+    float* sVec = reinterpret_cast<float*>(smem + Cfg::OFF_VEC);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+    uint64_t* kv_full = bars;           // [1]
+    uint64_t* qdo_full = bars + 1;      // [2]
+    uint64_t* qdo_empty = bars + 3;     // [2]
+    uint64_t* s_full = bars + 5;        // S^T and dP^T ready
+    uint64_t* pds_ready = bars + 6;     // count 128: P^T, dS^T in smem; S/dP TMEM drained
+    uint64_t* mma_done = bars + 7;      // (3)(4)(5) of a step retired: smem P/dS free, dQ^T readable
+    uint64_t* dq_free = bars + 8;       // count 128: dQ^T TMEM drained
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
+    const int k0 = j * BW_BK;
+    const int nq = p.S / BW_BQ;
+    const int i_start = p.causal ? (k0 / BW_BQ) : 0;
+    const int per_head = nq - i_start;
+    const int T = p.group * per_head;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmDO);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(kv_full, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1); }
+        mbar_init(s_full, 1); mbar_init(pds_ready, 128); mbar_init(mma_done, 1); mbar_init(dq_free, 128);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(kv_full, 2 * Cfg::KV_BYTES);
+#pragma unroll
+            for (int c = 0; c < BW_D / 64; ++c) {
+                tma_load_3d(&tmK, kv_full, sK + c * (BW_BK * 128), hk * BW_D + c * 64, k0, b);
+                tma_load_3d(&tmV, kv_full, sV + c * (BW_BK * 128), hk * BW_D + c * 64, k0, b);
+            }
+            for (int t = 0; t < T; ++t) {
+                const int st = t & 1; const uint32_t ph = (t >> 1) & 1;
+                const int h = hk * p.group + t / per_head;
+                const int q0 = (i_start + t % per_head) * BW_BQ;
+                mbar_wait(&qdo_empty[st], ph ^ 1);
+                mbar_expect_tx(&qdo_full[st], 2 * Cfg::QDO_BYTES + 2 * BW_BQ * 4);
+#pragma unroll
+                for (int c = 0; c < BW_D / 64; ++c) {
+                    tma_load_3d(&tmQ, &qdo_full[st], sQ + st * Cfg::QDO_BYTES + c * (BW_BQ * 128), h * BW_D + c * 64, q0, b);
+                    tma_load_3d(&tmDO, &qdo_full[st], sDO + st * Cfg::QDO_BYTES + c * (BW_BQ * 128), h * BW_D + c * 64, q0, b);
+                }
+                const size_t voff = ((size_t)b * p.Hq + h) * p.S + q0;
+                bulk_load_1d(sVec + st * 2 * BW_BQ, p.lse + voff, BW_BQ * 4, &qdo_full[st]);
+                bulk_load_1d(sVec + st * 2 * BW_BQ + BW_BQ, p.delta + voff, BW_BQ * 4, &qdo_full[st]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t id_s = make_idesc_bf16(128, BW_BQ, false, false);    // (1)(2): A,B K-major
+            constexpr uint32_t id_acc = make_idesc_bf16(128, BW_D, false, true);    // (3)(4): A K-major, B MN-major
+            constexpr uint32_t id_dq = make_idesc_bf16(128, BW_BQ, true, true);     // (5): A,B MN-major
+            const uint32_t ka = smem_u32(sK), va = smem_u32(sV), pa = smem_u32(sP), dsa = smem_u32(sDS);
+            mbar_wait(kv_full, 0);
+            for (int t = 0; t < T; ++t) {
+                const int st = t & 1;
+                mbar_wait(&qdo_full[st], (t >> 1) & 1);
+                tc_fence_after();
+                const uint32_t qa = smem_u32(sQ + st * Cfg::QDO_BYTES), doa = smem_u32(sDO + st * Cfg::QDO_BYTES);
+                // S/dP TMEM columns were drained before pds_ready(t-1), which this thread waited on in step t-1
+#pragma unroll
+                for (int k = 0; k < BW_D / 16; ++k) {
+                    const uint32_t offA = (k >> 2) * (BW_BK * 128) + (k & 3) * 32;
+                    const uint32_t offB = (k >> 2) * (BW_BQ * 128) + (k & 3) * 32;
+                    umma_bf16(tmem_base + Cfg::T_S, make_smem_desc(ka + offA, 0, 1024), make_smem_desc(qa + offB, 0, 1024),
+                              id_s, k > 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int k = 0; k < BW_D / 16; ++k) {
+                    const uint32_t offA = (k >> 2) * (BW_BK * 128) + (k & 3) * 32;
+                    const uint32_t offB = (k >> 2) * (BW_BQ * 128) + (k & 3) * 32;
+                    umma_bf16(tmem_base + Cfg::T_DP, make_smem_desc(va + offA, 0, 1024), make_smem_desc(doa + offB, 0, 1024),
+                              id_s, k > 0 ? 1u : 0u);
+                }
+                umma_commit(s_full);
+                mbar_wait(pds_ready, t & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < BW_BQ / 16; ++k) {          // (3) dV += P^T dO ; (4) dK += dS^T Q
+                    umma_bf16(tmem_base + Cfg::T_DV, make_smem_desc(pa + k * 32, 0, 1024),
+                              make_smem_desc(doa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
+                    umma_bf16(tmem_base + Cfg::T_DK, make_smem_desc(dsa + k * 32, 0, 1024),
+                              make_smem_desc(qa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
+                }
+                if (t > 0) { mbar_wait(dq_free, (t - 1) & 1); tc_fence_after(); }
+#pragma unroll
+                for (int k = 0; k < BW_BK / 16; ++k) {          // (5) dQ^T = K^T dS^T, contraction over the 128 keys
+                    umma_bf16(tmem_base + Cfg::T_DQ, make_smem_desc(ka + k * (16 * 128), BW_BK * 128, 1024),
+                              make_smem_desc(dsa + k * (16 * 128), BW_BK * 128, 1024), id_dq, k > 0 ? 1u : 0u);
+                }
+                umma_commit(&qdo_empty[st]);
+                umma_commit(mma_done);
+            }
+        }
+    } else if (warp >= 4) {
+        const int qd = warp & 3;
+        const int row = qd * 32 + lane;                  // key row (steps 1-4) / d index (step 5)
+        const uint32_t tb = tmem_base + ((uint32_t)(qd * 32) << 16);
+        const int key = k0 + row;
+        auto drain_dq = [&](int t) {
+            const int h = hk * p.group + t / per_head;
+            const int q0 = (i_start + t % per_head) * BW_BQ;
+            float* dst = p.dq + ((size_t)b * p.S + q0) * ((size_t)p.Hq * BW_D) + (size_t)h * BW_D + row;
+#pragma unroll 1
+            for (int c0 = 0; c0 < BW_BQ; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(tb + Cfg::T_DQ + c0, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 32; ++c)
+                    atomicAdd(dst + (size_t)(c0 + c) * ((size_t)p.Hq * BW_D), __uint_as_float(r[c]) * p.scale);
+            }
+        };
+        for (int t = 0; t < T; ++t) {
+            const int st = t & 1;
+            const int q0 = (i_start + t % per_head) * BW_BQ;
+            mbar_wait(&qdo_full[st], (t >> 1) & 1);      // lse/delta vectors landed (bulk copies on the same barrier)
+            mbar_wait(s_full, t & 1);
+            tc_fence_after();
+            const float* lse = sVec + st * 2 * BW_BQ;
+            const float* dl = lse + BW_BQ;
+            const bool diag = p.causal && (q0 < k0 + BW_BK);      // some (key > query) pairs in this tile
+            if (t > 0) mbar_wait(mma_done, (t - 1) & 1);          // smem P/dS free again; dQ^T(t-1) complete
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                uint32_t rs[32], rp[32];
+                tmem_ld32(tb + Cfg::T_S + half * 32, rs);
+                tmem_ld32(tb + Cfg::T_DP + half * 32, rp);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    float pv[8], dsv[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int c = half * 32 + c8 * 8 + e;
+                        float pe = exp2f(__uint_as_float(rs[c8 * 8 + e]) * p.scale_log2 - lse[c]);
+                        if (diag && key > q0 + c) pe = 0.f;
+                        pv[e] = pe;
+                        dsv[e] = pe * (__uint_as_float(rp[c8 * 8 + e]) - dl[c]);
+                    }
+                    uint4 up, ud;
+                    up.x = pack_bf16(pv[0], pv[1]); up.y = pack_bf16(pv[2], pv[3]); up.z = pack_bf16(pv[4], pv[5]); up.w = pack_bf16(pv[6], pv[7]);
+                    ud.x = pack_bf16(dsv[0], dsv[1]); ud.y = pack_bf16(dsv[2], dsv[3]); ud.z = pack_bf16(dsv[4], dsv[5]); ud.w = pack_bf16(dsv[6], dsv[7]);
+                    const int chunk = half * 4 + c8;
+                    const int off = row * 128 + ((chunk ^ (row & 7)) << 4);
+                    *reinterpret_cast<uint4*>(sP + off) = up;
+                    *reinterpret_cast<uint4*>(sDS + off) = ud;
+                }
+            }
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(pds_ready);
+            if (t > 0) {
+                drain_dq(t - 1);
+                tc_fence_before();
+                mbar_arrive(dq_free);
+            }
+        }
+        mbar_wait(mma_done, (T - 1) & 1);
+        tc_fence_after();
+        drain_dq(T - 1);
+        // ---- epilogue: dV_j, dK_j (x softmax scale) -> bf16 -> global rows [b*S + key], head hk
+        bf16* dvr = p.dv + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
+        bf16* dkr = p.dk + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BW_D; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld32(tb + Cfg::T_DV + c0, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int c8 = 0; c8 < 4; ++c8) {
+                uint4 u;
+                u.x = pack_bf16(__uint_as_float(r[c8 * 8 + 0]), __uint_as_float(r[c8 * 8 + 1]));
+                u.y = pack_bf16(__uint_as_float(r[c8 * 8 + 2]), __uint_as_float(r[c8 * 8 + 3]));
+                u.z = pack_bf16(__uint_as_float(r[c8 * 8 + 4]), __uint_as_float(r[c8 * 8 + 5]));
+                u.w = pack_bf16(__uint_as_float(r[c8 * 8 + 6]), __uint_as_float(r[c8 * 8 + 7]));
+                *reinterpret_cast<uint4*>(dvr + c0 + c8 * 8) = u;
+            }
+            tmem_ld32(tb + Cfg::T_DK + c0, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int c8 = 0; c8 < 4; ++c8) {
+                uint4 u;
+                u.x = pack_bf16(__uint_as_float(r[c8 * 8 + 0]) * p.scale, __uint_as_float(r[c8 * 8 + 1]) * p.scale);
+                u.y = pack_bf16(__uint_as_float(r[c8 * 8 + 2]) * p.scale, __uint_as_float(r[c8 * 8 + 3]) * p.scale);
+                u.z = pack_bf16(__uint_as_float(r[c8 * 8 + 4]) * p.scale, __uint_as_float(r[c8 * 8 + 5]) * p.scale);
+                u.w = pack_bf16(__uint_as_float(r[c8 * 8 + 6]) * p.scale, __uint_as_float(r[c8 * 8 + 7]) * p.scale);
+                *reinterpret_cast<uint4*>(dkr + c0 + c8 * 8) = u;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) { tc_fence_after(); tmem_dealloc<Cfg::TMEM_COLS>(tmem_base); }
+}
+
+// Delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]; one warp per (row, head), D = 128 -> 4 elements per lane
+__global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dO, int ld, float* __restrict__ delta,
+                                  long long rows, int S, int Hq) {
+    const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= rows * Hq) return;
+    const long long r = w / Hq; const int h = (int)(w % Hq);
+    const size_t off = (size_t)r * ld + h * BW_D + lane * 4;
+    const uint2 a = *reinterpret_cast<const uint2*>(o + off), g = *reinterpret_cast<const uint2*>(dO + off);
+    const float2 a0 = unpack_bf16(a.x), a1 = unpack_bf16(a.y), g0 = unpack_bf16(g.x), g1 = unpack_bf16(g.y);
+    float s = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y;
+    s = warp_sum(s);
+    if (lane == 0) delta[((size_t)(r / S) * Hq + h) * S + (r % S)] = s;
+}
+
+static int bw_tmap(CUtensorMap* m, const void* ptr, int cols, int S, int B, int ld, int box_rows) {
+    unsigned long long dims[3] = {(unsigned long long)cols, (unsigned long long)S, (unsigned long long)B};
+    unsigned long long strides[2] = {(unsigned long long)ld * 2ull, (unsigned long long)S * ld * 2ull};
+    unsigned int box[3] = {64u, (unsigned int)box_rows, 1u};
+    return encode_tmap_bf16(m, ptr, 3, dims, strides, box);
+}
+
+}  // namespace vlb
+
+using namespace vlb;
+
+extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_qkv, const void* o, const void* d_o,
+                            int ld_o, const void* lse_f32, void* delta_f32, void* dq_f32, void* dk, void* dv, int ld_dkv,
+                            int B, int S, int Hq, int Hkv, int D, int causal, float scale, void* stream) {
+    VLB_REQUIRE(D == BW_D, "attn_bwd: only head_dim 128 (decoder) is implemented, got %d", D);
+    VLB_REQUIRE(Hkv > 0 && Hq % Hkv == 0 && S % BW_BK == 0, "attn_bwd: Hq=%d Hkv=%d S=%d (S must be a multiple of 128)",
+                Hq, Hkv, S);
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long rows = (long long)B * S;
+    {
+        const long long threads = rows * Hq * 32;
+        attn_delta_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>((const bf16*)o, (const bf16*)d_o, ld_o,
+                                                                             (float*)delta_f32, rows, S, Hq);
+        int rc = check_launch("attn_delta_kernel");
+        if (rc) return rc;
+    }
+    cudaError_t e = cudaMemsetAsync(dq_f32, 0, (size_t)rows * Hq * D * sizeof(float), st);
+    VLB_REQUIRE(e == cudaSuccess, "attn_bwd memset: %s", cudaGetErrorString(e));
+    CUtensorMap tq, tk, tv, tdo;
+    int rc;
+    if ((rc = bw_tmap(&tq, q, Hq * D, S, B, ld_qkv, BW_BQ))) return rc;
+    if ((rc = bw_tmap(&tk, k, Hkv * D, S, B, ld_qkv, BW_BK))) return rc;
+    if ((rc = bw_tmap(&tv, v, Hkv * D, S, B, ld_qkv, BW_BK))) return rc;
+    if ((rc = bw_tmap(&tdo, d_o, Hq * D, S, B, ld_o, BW_BQ))) return rc;
+    BwParams p;
+    p.S = S; p.Hq = Hq; p.Hkv = Hkv; p.group = Hq / Hkv; p.causal = causal;
+    p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+    p.lse = (const float*)lse_f32; p.delta = (const float*)delta_f32; p.dq = (float*)dq_f32;
+    p.dk = (bf16*)dk; p.dv = (bf16*)dv; p.ld_dkv = ld_dkv;
+    static bool attr = false;
+    if (!attr) {
+        e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwCfg::SMEM_BYTES);
+        VLB_REQUIRE(e == cudaSuccess, "attn_bwd smem attr: %s", cudaGetErrorString(e));
+        attr = true;
+    }
+    dim3 grid(S / BW_BK, Hkv, B);
+    attn_bwd_kernel<<<grid, BW_THREADS, BwCfg::SMEM_BYTES, st>>>(p, tq, tk, tv, tdo);
+    return check_launch("attn_bwd_kernel");
+}

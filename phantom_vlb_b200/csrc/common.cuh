@@ -158,6 +158,12 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, const void* smem,
                  : "memory");
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// 1-D bulk copy global -> shared (bytes % 16 == 0, both addresses 16-byte aligned), completes on an mbarrier
+__device__ __forceinline__ void bulk_load_1d(void* smem, const void* gptr, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(gptr)), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 __device__ __forceinline__ void tma_load_3d(const void* tmap, uint64_t* bar, void* smem, int x, int y, int z) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"

@@ -61,3 +61,23 @@ def attn_fwd(qkv, B, S, Hq, Hkv, D, causal, scale=None, out=None, need_lse=True)
     _l.call("vlb_attn_fwd", base, base + Hq * D * es, base + (Hq + Hkv) * D * es, qkv.stride(0), _l.ptr(out),
             out.stride(0), _l.ptr(lse), B, S, Hq, Hkv, D, int(causal), float(scale), _l.cur_stream())
     return out, lse
+
+
+def attn_bwd(qkv, o, do, lse, B, S, Hq, Hkv, D, causal, scale=None, dqkv=None, dq_f32=None, delta=None):
+    """Backward of attn_fwd. Returns (dq_f32 [B*S, Hq*D] fp32, dqkv bf16 with the k/v gradient columns filled)."""
+    _chk(qkv, torch.bfloat16), _chk(o, torch.bfloat16), _chk(do, torch.bfloat16)
+    dev = qkv.device
+    if dqkv is None:
+        dqkv = torch.empty_like(qkv)
+    if dq_f32 is None:
+        dq_f32 = torch.empty((B * S, Hq * D), device=dev, dtype=torch.float32)
+    if delta is None:
+        delta = torch.empty((B, Hq, S), device=dev, dtype=torch.float32)
+    if scale is None:
+        scale = D ** -0.5
+    assert o.stride(0) == do.stride(0)
+    base, dbase, es = qkv.data_ptr(), dqkv.data_ptr(), 2
+    _l.call("vlb_attn_bwd", base, base + Hq * D * es, base + (Hq + Hkv) * D * es, qkv.stride(0), _l.ptr(o), _l.ptr(do),
+            o.stride(0), _l.ptr(lse), _l.ptr(delta), _l.ptr(dq_f32), dbase + Hq * D * es, dbase + (Hq + Hkv) * D * es,
+            dqkv.stride(0), B, S, Hq, Hkv, D, int(causal), float(scale), _l.cur_stream())
+    return dq_f32, dqkv

@@ -51,3 +51,27 @@ def test_attn_fwd_large_logits():
     torch.cuda.synchronize()
     ro, _ = _ref(qkv, B, S, Hq, Hkv, D, True)
     assert (o.float() - ro).abs().max().item() < 3e-2
+
+
+@pytest.mark.parametrize("B,S,Hq,Hkv,causal", [(1, 128, 1, 1, True), (1, 256, 2, 1, True), (2, 512, 8, 2, True),
+                                               (1, 1024, 4, 1, True), (1, 256, 2, 2, False)])
+def test_attn_bwd(B, S, Hq, Hkv, causal):
+    from phantom_vlb_b200 import ops
+    D = 128
+    torch.manual_seed(S * 3 + Hq)
+    qkv = torch.randn(B * S, (Hq + 2 * Hkv) * D, device="cuda").bfloat16()
+    do = torch.randn(B * S, Hq * D, device="cuda").bfloat16()
+    o, lse = ops.attn_fwd(qkv, B, S, Hq, Hkv, D, causal)
+    dq, dqkv = ops.attn_bwd(qkv, o, do, lse, B, S, Hq, Hkv, D, causal)
+    torch.cuda.synchronize()
+    x = qkv.float().requires_grad_(True)
+    ro, _ = _ref(x, B, S, Hq, Hkv, D, causal)
+    (ro * do.float()).sum().backward()
+    g = x.grad
+    rq, rk, rv = g.split([Hq * D, Hkv * D, Hkv * D], dim=1)
+    dk = dqkv[:, Hq * D:(Hq + Hkv) * D].float()
+    dv = dqkv[:, (Hq + Hkv) * D:].float()
+    for name, a, r in (("dq", dq, rq), ("dk", dk, rk), ("dv", dv, rv)):
+        err = (a - r).abs().max().item()
+        scale = r.abs().max().item()
+        assert err < 2e-2 * scale + 1e-3, "%s max err %g (scale %g)" % (name, err, scale)
