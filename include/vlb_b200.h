@@ -106,6 +106,28 @@ int vlb_hrf_pool_bwd(const void* x, const void* norm_w, const void* ln1_w, const
                      const void* dpooled_f32, void* dx, void* dg1_f32, void* db1_f32, int B, int S, int H,
                      int nch, float eps_rms, float eps_ln, void* stream);
 
+/* ------------------------------------------------------------------ optimiser (one flat buffer of trainables)
+ * clip_grad_norm_(gradient_clip_val=1) + AdamW (decoupled weight decay on every trainable) with the cosine LR value
+ * passed per step; writes the bf16 working copy consumed by the GEMMs in the same sweep. grad_scale = 1/world_size
+ * folds the data-parallel mean. (src/litmodule/videollama2_vlb_litmodule.py:345-379; experiment yaml :46) */
+int vlb_grad_sumsq(const void* grad_f32, long long n, void* acc_f32, void* stream);
+int vlb_adamw_step(void* param_f32, const void* grad_f32, void* m_f32, void* v_f32, void* param_bf16,
+                   long long n, const void* sumsq_f32, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, int step, float max_norm, float grad_scale, void* stream);
+int vlb_f32_to_bf16(const void* src, void* dst, long long n, void* stream);
+int vlb_copy2d(const void* src, int lds, void* dst, int ldd, int rows, int cols, int transpose, void* stream);
+
+/* ------------------------------------------------------------------ per-parcel Pearson r (single pass, fp64 moments)
+ * stats_f64 [5, P] accumulates (sum x, sum y, sum x^2, sum y^2, sum xy) of nan_to_num'd inputs; the raw sums are
+ * additive, so row shards on different GPUs merge with one all-reduce(sum) before finalize.
+ * Replaces torchmetrics PearsonCorrCoef in LogValAccuracyCallback (src/utils.py:101-110); vlb_paint_labels is the
+ * parcel -> voxel gather of make_acc_brainmaps (src/postprocessing/make_acc_brainmaps.py:50-53). */
+int vlb_pearson_update(const void* preds, const void* targets, void* stats_f64, long long N, long long P,
+                       int is_bf16, void* stream);
+int vlb_pearson_finalize(const void* stats_f64, long long n_rows, void* r_f32, long long P, void* stream);
+int vlb_paint_labels(const void* r_f32, const void* labels_i32, void* vol_f32, long long V, int P, int square,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,217 @@
+"""Training-step engine: runs the phantom_vlb hot path (VLBLitModule.training_step + backward + optimiser step,
+src/litmodule/videollama2_vlb_litmodule.py:259-306, 345-379) as an explicit sequence of libvlb_b200 kernel launches
+on the current CUDA stream. PyTorch only owns the device buffers; every arithmetic op below is a C-ABI call.
+
+Forward  : ViT frames (no grad) -> STC connector (no grad) -> <video> splice -> L decoder layers with LoRA fused
+           into the base GEMMs -> final RMSNorm + LN1 + HRF pooling + LN2 -> readout GEMM -> MSE + ridge penalty.
+Backward : head -> decoder layers in reverse (dX through the frozen weights, rank-r dA/dB written straight into the
+           flat fp32 gradient buffer) -> stops at the spliced embeddings (tower, connector, embeddings are frozen).
+"""
+import math
+
+import torch
+
+from . import lib as _l
+from . import ops
+from .model import ModelConfig, Trainables
+from .ops import ACT_GELU, ACT_NONE, ACT_QUICK_GELU, ACT_SIGMOID, ACT_SILU
+
+
+class Engine:
+    def __init__(self, cfg: ModelConfig, frozen, trainables: Trainables = None, device="cuda", dropout_rate=0.0,
+                 lora_dropout=0.0):
+        _l.call("vlb_check_device")
+        self.cfg, self.W, self.dev = cfg, frozen, torch.device(device)
+        self.T = trainables if trainables is not None else Trainables(cfg, self.dev)
+        self.scale = cfg.lora_alpha / cfg.lora_r
+        self.dropout_rate = float(dropout_rate)
+        if lora_dropout:
+            raise NotImplementedError("lora_dropout > 0 is not implemented (parity and benchmark runs use 0)")
+        self.saved = None
+        self.launches = 0
+        self._bufs = {}
+
+    # ------------------------------------------------------------------ buffers
+    def buf(self, name, shape, dtype=torch.bfloat16):
+        """Persistent workspace keyed by name (re-used across steps so TMA descriptors stay cached)."""
+        key = (name, tuple(shape), dtype)
+        t = self._bufs.get(key)
+        if t is None:
+            t = torch.empty(shape, device=self.dev, dtype=dtype)
+            self._bufs[key] = t
+        return t
+
+    def gemm(self, a, b, out, **kw):
+        self.launches += 1
+        return ops.gemm(a, b, out, **kw)
+
+    # ------------------------------------------------------------------ vision tower (frozen, forward only)
+    def vit_forward(self, pixels):
+        """pixels fp32 [N, 3, H, W] -> patch features bf16 [N*G*G, Hv] (hidden_states[-2][:, 1:], encoder.py:31-53)."""
+        cfg, W = self.cfg, self.W
+        N = pixels.shape[0]
+        G2, Hv, T = cfg.grid ** 2, cfg.vit_hidden, cfg.grid ** 2 + 1
+        cols = ops.patch_im2col(pixels, cfg.patch_size, cfg.kpad, self.buf("vit_cols", (N * G2, cfg.kpad)))
+        patch = self.gemm(cols, W.vit["patch_w"], self.buf("vit_patch", (N * G2, Hv)))
+        h = ops.clip_embed(patch, W.vit["cls"], W.vit["pos"], W.vit["pre_w"], W.vit["pre_b"], N, T, cfg.vit_ln_eps,
+                           self.buf("vit_h", (N * T, Hv)))
+        y = self.buf("vit_y", (N * T, Hv))
+        qkv = self.buf("vit_qkv", (N * T, 3 * Hv))
+        o = self.buf("vit_o", (N * T, Hv))
+        f = self.buf("vit_f", (N * T, cfg.vit_mlp))
+        h2 = self.buf("vit_h2", (N * T, Hv))
+        hd = Hv // cfg.vit_heads
+        for L in W.vit_layers:
+            ops.layernorm_fwd(h, L["ln1_w"], L["ln1_b"], cfg.vit_ln_eps, out=y)
+            self.gemm(y, L["wqkv"], qkv, bias=L["bqkv"])
+            ops.attn_fwd(qkv, N, T, cfg.vit_heads, cfg.vit_heads, hd, False, out=o, need_lse=False)
+            self.gemm(o, L["wo"], h2, bias=L["bo"], residual=h)
+            ops.layernorm_fwd(h2, L["ln2_w"], L["ln2_b"], cfg.vit_ln_eps, out=y)
+            self.gemm(y, L["fc1_w"], f, bias=L["fc1_b"], act=ACT_QUICK_GELU)
+            self.gemm(f, L["fc2_w"], h, bias=L["fc2_b"], residual=h2)
+            self.launches += 3
+        self.launches += 4
+        return ops.drop_cls(h, N, T, self.buf("vit_feats", (N * G2, Hv)))
+
+    # ------------------------------------------------------------------ STC connector (frozen, forward only)
+    def _stc_block(self, x, blk, F, Hh, Ww, tag, idx):
+        cfg = self.cfg
+        C, HW, eps = cfg.hidden, Hh * Ww, cfg.stc_ln_eps
+        M = F * HW
+        a = self.gemm(x, blk["conv1_w"], self.buf(tag + "a", (M, C)))
+        ops.layernorm_fwd(a, blk["n1_w"], blk["n1_b"], eps, act=ACT_SILU, out=a)
+        b = ops.dwconv3x3(a, blk["dw_w"], F, Hh, Ww, self.buf(tag + "b", (M, C)))
+        ops.layernorm_fwd(b, blk["n2_w"], blk["n2_b"], eps, act=ACT_SILU, out=b)
+        pool = ops.se_pool(b, F, HW, self.buf(tag + "pool", (F, C)))
+        rd = blk["se1_w"].shape[0]
+        g1 = self.gemm(pool, blk["se1_w"], self.buf(tag + "g1_%d" % rd, (F, rd)), bias=blk["se1_b"], act=ACT_SILU)
+        gate = self.gemm(g1, blk["se2_w"], self.buf(tag + "gate", (F, C)), bias=blk["se2_b"], act=ACT_SIGMOID)
+        ops.se_scale(b, gate, F, HW, out=b)
+        c = self.gemm(b, blk["conv3_w"], self.buf(tag + "c", (M, C)))
+        if blk["ds_w"] is not None:
+            sc = self.gemm(x, blk["ds_w"], self.buf(tag + "sc", (M, C)))
+            ops.layernorm_fwd(sc, blk["dsn_w"], blk["dsn_b"], eps, out=sc)
+        else:
+            sc = x
+        out = self.buf(tag + "out%d" % (idx & 1), (M, C))       # ping-pong: never aliases the block input
+        ops.layernorm_fwd(c, blk["n3_w"], blk["n3_b"], eps, residual=sc, act=ACT_SILU, out=out)
+        self.launches += 7
+        return out
+
+    def stc_forward(self, feats, B):
+        """feats [B*T*G*G, Hv] -> visual tokens [B*Nv, H] (STCConnector.forward, projector.py:189-215)."""
+        cfg, W = self.cfg, self.W
+        T, G, C = cfg.num_frames, cfg.grid, cfg.hidden
+        x = feats
+        for i, blk in enumerate(W.stc["s1"]):
+            x = self._stc_block(x, blk, B * T, G, G, "s1_", i)
+        cols = ops.conv3d_gather(x, B, T, G, G, self.buf("stc_cols", (B * cfg.n_vis, 8 * C)))
+        x = self.gemm(cols, W.stc["sampler_w"], self.buf("stc_samp", (B * cfg.n_vis, C)), bias=W.stc["sampler_b"], act=ACT_SILU)
+        for i, blk in enumerate(W.stc["s2"]):
+            x = self._stc_block(x, blk, B * cfg.t_out, cfg.grid_out, cfg.grid_out, "s2_", i)
+        r1 = self.gemm(x, W.stc["ro1_w"], self.buf("stc_r1", (B * cfg.n_vis, C)), bias=W.stc["ro1_b"], act=ACT_GELU)
+        self.launches += 1
+        return self.gemm(r1, W.stc["ro2_w"], self.buf("stc_vis", (B * cfg.n_vis, C)), bias=W.stc["ro2_b"])
+
+    # ------------------------------------------------------------------ decoder (LoRA fused), forward
+    def _layer_bufs(self, l, M):
+        cfg = self.cfg
+        H, I, D, r = cfg.hidden, cfg.mlp, cfg.head_dim, cfg.lora_r
+        nqkv = (cfg.heads + 2 * cfg.kv_heads) * D
+        t = "L%d_" % l
+        B = M // cfg.max_len
+        return dict(
+            x=self.buf(t + "x", (M, H)), rstd1=self.buf(t + "rstd1", (M,), torch.float32), xn1=self.buf(t + "xn1", (M, H)),
+            xa1=self.buf(t + "xa1", (M, 3 * r)), qkv=self.buf(t + "qkv", (M, nqkv)), o=self.buf(t + "o", (M, cfg.heads * D)),
+            lse=self.buf(t + "lse", (B, cfg.heads, cfg.max_len), torch.float32), xa2=self.buf(t + "xa2", (M, r)),
+            h1=self.buf(t + "h1", (M, H)), rstd2=self.buf(t + "rstd2", (M,), torch.float32), xn2=self.buf(t + "xn2", (M, H)),
+            xa3=self.buf(t + "xa3", (M, 2 * r)), gu=self.buf(t + "gu", (M, 2 * I)), act=self.buf(t + "act", (M, I)),
+            xa4=self.buf(t + "xa4", (M, r)))
+
+    def decoder_forward(self, x0, B, save=True):
+        """x0 [B*S, H] (buffer L0_x) -> pre-final-norm hidden [B*S, H]."""
+        cfg, W, T = self.cfg, self.W, self.T
+        S, M, D, s = cfg.max_len, B * cfg.max_len, cfg.head_dim, self.scale
+        x = x0
+        for l, L in enumerate(W.llm_layers):
+            b = self._layer_bufs(l if save else 0, M)
+            p = "layers.%d." % l
+            bc = T.bcat[l]
+            nxt = self.buf("L%d_x" % (l + 1), (M, cfg.hidden)) if save else self.buf("Lx_%d" % (l & 1), (M, cfg.hidden))
+            ops.rmsnorm_fwd(x, L["ln1_w"], cfg.rms_eps, out=b["xn1"], rstd=b["rstd1"])
+            self.gemm(b["xn1"], T.w(p + "Acat_qkv"), b["xa1"], alpha=s)
+            self.gemm(b["xn1"], L["wqkv"], b["qkv"], a2=b["xa1"], b2=bc["qkv"])
+            ops.rope_(b["qkv"], W.llm["cos"], W.llm["sin"], S, cfg.heads + cfg.kv_heads, D)
+            ops.attn_fwd_into(b["qkv"], b["o"], b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True)
+            self.gemm(b["o"], T.w(p + "A_o"), b["xa2"], alpha=s)
+            self.gemm(b["o"], L["wo"], b["h1"], a2=b["xa2"], b2=bc["o"], residual=x)
+            ops.rmsnorm_fwd(b["h1"], L["ln2_w"], cfg.rms_eps, out=b["xn2"], rstd=b["rstd2"])
+            self.gemm(b["xn2"], T.w(p + "Acat_gu"), b["xa3"], alpha=s)
+            self.gemm(b["xn2"], L["wgu"], b["gu"], a2=b["xa3"], b2=bc["gu"])
+            ops.swiglu_fwd(b["gu"], out=b["act"])
+            self.gemm(b["act"], T.w(p + "A_d"), b["xa4"], alpha=s)
+            self.gemm(b["act"], L["wd"], nxt, a2=b["xa4"], b2=bc["d"], residual=b["h1"])
+            self.launches += 5
+            x = nxt
+        return x
+
+    # ------------------------------------------------------------------ decoder backward
+    def decoder_backward(self, dx, B):
+        """dx: gradient wrt the pre-final-norm hidden [B*S, H] (bf16). Fills LoRA gradients in T.grad."""
+        cfg, W, T = self.cfg, self.W, self.T
+        S, M, D, s, r = cfg.max_len, B * cfg.max_len, cfg.head_dim, self.scale, cfg.lora_r
+        H, I = cfg.hidden, cfg.mlp
+        nq, nkv = cfg.heads * D, cfg.kv_heads * D
+        dact = self.buf("bw_dact", (M, I))
+        dgu = self.buf("bw_dgu", (M, 2 * I))
+        dxn = self.buf("bw_dxn", (M, H))
+        dh1 = self.buf("bw_dh1", (M, H))
+        do = self.buf("bw_do", (M, nq))
+        dqkv = self.buf("bw_dqkv", (M, nq + 2 * nkv))
+        dq32 = self.buf("bw_dq32", (M, nq), torch.float32)
+        delta = self.buf("bw_delta", (B, cfg.heads, S), torch.float32)
+        t48 = self.buf("bw_t48", (M, 3 * r))
+        t32 = self.buf("bw_t32", (M, 2 * r))
+        t16 = self.buf("bw_t16", (M, r))
+        dxa = self.buf("bw_dx_a", (M, H))
+        dxb = self.buf("bw_dx_b", (M, H))
+        for l in range(cfg.layers - 1, -1, -1):
+            L, b, bc = W.llm_layers[l], self._layer_bufs(l, M), T.bcat[l]
+            p = "layers.%d." % l
+            x = self.buf("L%d_x" % l, (M, H))
+            # ---- down_proj: x_next = h1 + act Wd^T + s (act A_d^T) B_d^T
+            self.gemm(dx, bc["d"], t16, b_mn=True, alpha=s)
+            self.gemm(dx, L["wd"], dact, a2=t16, b2=T.w(p + "A_d"), b_mn=True)
+            self.gemm(t16, b["act"], T.g(p + "A_d"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(b["xa4"], dx, T.g(p + "Bt_d"), a_mn=True, b_mn=True, out_f32=True)
+            ops.swiglu_bwd(b["gu"], dact, out=dgu)
+            # ---- gate/up
+            self.gemm(dgu, bc["gu"], t32, b_mn=True, alpha=s)
+            self.gemm(dgu, L["wgu"], dxn, a2=t32, b2=T.w(p + "Acat_gu"), b_mn=True)
+            self.gemm(t32, b["xn2"], T.g(p + "Acat_gu"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(b["xa3"][:, 0:r], dgu[:, 0:I], T.g(p + "Bt_g"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(b["xa3"][:, r:2 * r], dgu[:, I:2 * I], T.g(p + "Bt_u"), a_mn=True, b_mn=True, out_f32=True)
+            ops.rmsnorm_bwd(dxn, b["h1"], L["ln2_w"], b["rstd2"], dres=dx, out=dh1)
+            # ---- o_proj: h1 = x + o Wo^T + s (o A_o^T) B_o^T
+            self.gemm(dh1, bc["o"], t16, b_mn=True, alpha=s)
+            self.gemm(dh1, L["wo"], do, a2=t16, b2=T.w(p + "A_o"), b_mn=True)
+            self.gemm(t16, b["o"], T.g(p + "A_o"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(b["xa2"], dh1, T.g(p + "Bt_o"), a_mn=True, b_mn=True, out_f32=True)
+            # ---- attention + RoPE
+            ops.attn_bwd(b["qkv"], b["o"], do, b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True, dqkv=dqkv, dq_f32=dq32,
+                         delta=delta)
+            ops.rope_bwd_f32(dq32, dqkv, W.llm["cos"], W.llm["sin"], S, cfg.heads, D)
+            ops.rope_(dqkv[:, nq:], W.llm["cos"], W.llm["sin"], S, cfg.kv_heads, D, inverse=True)
+            # ---- q/k/v
+            self.gemm(dqkv, bc["qkv"], t48, b_mn=True, alpha=s)
+            self.gemm(t48, b["xn1"], T.g(p + "Acat_qkv"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(b["xa1"][:, 0:r], dqkv[:, 0:nq], T.g(p + "Bt_q"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True)
+            self.launches += 7
+            if l > 0:        # the spliced embeddings are frozen: layer 0 needs no input gradient
+                self.gemm(dqkv, L["wqkv"], dxn, a2=t48, b2=T.w(p + "Acat_qkv"), b_mn=True)
+                nxt = dxa if dx.data_ptr() != dxa.data_ptr() else dxb
+                ops.rmsnorm_bwd(dxn, x, L["ln1_w"], b["rstd1"], dres=dh1, out=nxt)
+                self.launches += 1
+                dx = nxt

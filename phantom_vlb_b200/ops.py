@@ -3,7 +3,7 @@ import torch
 
 from . import lib as _l
 
-ACT_NONE, ACT_QUICK_GELU, ACT_GELU, ACT_SILU = 0, 1, 2, 3
+ACT_NONE, ACT_QUICK_GELU, ACT_GELU, ACT_SILU, ACT_SIGMOID = 0, 1, 2, 3, 4
 
 
 def _chk(t, dtype=None):
@@ -81,3 +81,176 @@ def attn_bwd(qkv, o, do, lse, B, S, Hq, Hkv, D, causal, scale=None, dqkv=None, d
             o.stride(0), _l.ptr(lse), _l.ptr(delta), _l.ptr(dq_f32), dbase + Hq * D * es, dbase + (Hq + Hkv) * D * es,
             dqkv.stride(0), B, S, Hq, Hkv, D, int(causal), float(scale), _l.cur_stream())
     return dq_f32, dqkv
+
+
+# ------------------------------------------------------------------------------------------------ row kernels
+def _st():
+    return _l.cur_stream()
+
+
+def rmsnorm_fwd(x, w, eps, out=None, rstd=None):
+    M, H = x.shape
+    out = torch.empty_like(x) if out is None else out
+    _l.call("vlb_rmsnorm_fwd", _l.ptr(x), _l.ptr(w), _l.ptr(out), _l.ptr(rstd), M, H, float(eps), _st())
+    return out
+
+
+def rmsnorm_bwd(dy, x, w, rstd, dres=None, out=None):
+    M, H = x.shape
+    out = torch.empty_like(x) if out is None else out
+    _l.call("vlb_rmsnorm_bwd", _l.ptr(dy), _l.ptr(x), _l.ptr(w), _l.ptr(rstd), _l.ptr(dres), _l.ptr(out), M, H, _st())
+    return out
+
+
+def layernorm_fwd(x, w, b, eps, residual=None, act=ACT_NONE, out=None):
+    M, H = x.shape
+    out = torch.empty_like(x) if out is None else out
+    _l.call("vlb_layernorm_fwd", _l.ptr(x), _l.ptr(w), _l.ptr(b), _l.ptr(residual), _l.ptr(out), M, H, float(eps),
+            int(act), _st())
+    return out
+
+
+def rope_(qkv, cos, sin, S, nheads, D, inverse=False):
+    _l.call("vlb_rope", _l.ptr(qkv), qkv.stride(0), _l.ptr(cos), _l.ptr(sin), qkv.shape[0], S, nheads, D, int(inverse), _st())
+    return qkv
+
+
+def rope_bwd_f32(dq_f32, dqkv, cos, sin, S, nheads, D):
+    _l.call("vlb_rope_bwd_f32", _l.ptr(dq_f32), _l.ptr(dqkv), dqkv.stride(0), _l.ptr(cos), _l.ptr(sin), dqkv.shape[0], S,
+            nheads, D, _st())
+    return dqkv
+
+
+def swiglu_fwd(gu, out=None):
+    M, I2 = gu.shape
+    out = torch.empty((M, I2 // 2), device=gu.device, dtype=gu.dtype) if out is None else out
+    _l.call("vlb_swiglu_fwd", _l.ptr(gu), _l.ptr(out), M, I2 // 2, _st())
+    return out
+
+
+def swiglu_bwd(gu, dact, out=None):
+    M, I2 = gu.shape
+    out = torch.empty_like(gu) if out is None else out
+    _l.call("vlb_swiglu_bwd", _l.ptr(gu), _l.ptr(dact), _l.ptr(out), M, I2 // 2, _st())
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ vision / splice
+def patch_im2col(pixels, patch, kpad, out=None):
+    N, C, H, W = pixels.shape
+    assert C == 3 and H == W and pixels.dtype == torch.float32 and pixels.is_contiguous()
+    G = H // patch
+    out = torch.empty((N * G * G, kpad), device=pixels.device, dtype=torch.bfloat16) if out is None else out
+    _l.call("vlb_patch_im2col", _l.ptr(pixels), _l.ptr(out), N, H, patch, kpad, _st())
+    return out
+
+
+def clip_embed(patch, cls, pos, lnw, lnb, N, T, eps, out=None):
+    H = patch.shape[1]
+    out = torch.empty((N * T, H), device=patch.device, dtype=torch.bfloat16) if out is None else out
+    _l.call("vlb_clip_embed", _l.ptr(patch), _l.ptr(cls), _l.ptr(pos), _l.ptr(lnw), _l.ptr(lnb), _l.ptr(out), N, T, H,
+            float(eps), _st())
+    return out
+
+
+def drop_cls(x, N, T, out=None):
+    H = x.shape[1]
+    out = torch.empty((N * (T - 1), H), device=x.device, dtype=x.dtype) if out is None else out
+    _l.call("vlb_drop_cls", _l.ptr(x), _l.ptr(out), N, T, H, _st())
+    return out
+
+
+def dwconv3x3(x, w9c, F, Hh, Ww, out=None):
+    C = x.shape[1]
+    out = torch.empty_like(x) if out is None else out
+    _l.call("vlb_dwconv3x3", _l.ptr(x), _l.ptr(w9c), _l.ptr(out), F, Hh, Ww, C, _st())
+    return out
+
+
+def se_pool(x, F, HW, out=None):
+    C = x.shape[1]
+    out = torch.empty((F, C), device=x.device, dtype=x.dtype) if out is None else out
+    _l.call("vlb_se_pool", _l.ptr(x), _l.ptr(out), F, HW, C, _st())
+    return out
+
+
+def se_scale(x, gate, F, HW, out=None):
+    C = x.shape[1]
+    out = torch.empty_like(x) if out is None else out
+    _l.call("vlb_se_scale", _l.ptr(x), _l.ptr(gate), _l.ptr(out), F, HW, C, _st())
+    return out
+
+
+def conv3d_gather(x, B, T, Hh, Ww, out=None):
+    C = x.shape[1]
+    To, Ho, Wo = T // 2 + 1, Hh // 2 + 1, Ww // 2 + 1
+    out = torch.empty((B * To * Ho * Wo, 8 * C), device=x.device, dtype=x.dtype) if out is None else out
+    _l.call("vlb_conv3d_gather", _l.ptr(x), _l.ptr(out), B, T, Hh, Ww, C, _st())
+    return out
+
+
+def ids_to_long(ids_f32):
+    out = torch.empty(ids_f32.shape, device=ids_f32.device, dtype=torch.int64)
+    _l.call("vlb_ids_to_long", _l.ptr(ids_f32), _l.ptr(out), ids_f32.numel(), _st())
+    return out
+
+
+def splice_embed(ids, table, vis, Nv, video_id=-201, out=None):
+    B, L = ids.shape
+    V, H = table.shape
+    S = L + Nv - 1
+    out = torch.empty((B * S, H), device=table.device, dtype=table.dtype) if out is None else out
+    pos = torch.empty((B,), device=table.device, dtype=torch.int32)
+    _l.call("vlb_splice_embed", _l.ptr(ids), _l.ptr(table), _l.ptr(vis), _l.ptr(out), _l.ptr(pos), B, L, Nv, H, V,
+            int(video_id), _st())
+    return out, pos
+
+
+def weight_mask(padvals, vis_w, lang_w, tok_per_frame, S):
+    B, Tp = vis_w.shape
+    assert padvals.dtype == torch.int64 and vis_w.dtype == torch.float64 and lang_w.dtype == torch.float64
+    out = torch.empty((B, S), device=vis_w.device, dtype=torch.float32)
+    _l.call("vlb_weight_mask", _l.ptr(padvals), _l.ptr(vis_w), _l.ptr(lang_w), _l.ptr(out), B, Tp, tok_per_frame,
+            lang_w.shape[1], S, _st())
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ optimiser / pearson
+def copy2d(src, dst, rows, cols, transpose=False):
+    _l.call("vlb_copy2d", _l.ptr(src), src.stride(0), _l.ptr(dst), dst.stride(0), rows, cols, int(transpose), _st())
+    return dst
+
+
+def pearson(preds, targets, stats=None, finalize=True):
+    """Per-column Pearson r of [N,P] tensors (bf16 or fp32). Returns (r fp32 [P] or None, stats fp64 [5,P])."""
+    N, P = preds.shape
+    assert preds.dtype == targets.dtype and preds.is_contiguous() and targets.is_contiguous()
+    if stats is None:
+        stats = torch.zeros((5, P), device=preds.device, dtype=torch.float64)
+    _l.call("vlb_pearson_update", _l.ptr(preds), _l.ptr(targets), _l.ptr(stats), N, P,
+            int(preds.dtype == torch.bfloat16), _st())
+    r = pearson_finalize(stats, N) if finalize else None
+    return r, stats
+
+
+def pearson_finalize(stats, n_rows):
+    P = stats.shape[1]
+    r = torch.empty((P,), device=stats.device, dtype=torch.float32)
+    _l.call("vlb_pearson_finalize", _l.ptr(stats), int(n_rows), _l.ptr(r), P, _st())
+    return r
+
+
+def paint_labels(r, labels, square=True):
+    vol = torch.empty(labels.shape, device=r.device, dtype=torch.float32)
+    _l.call("vlb_paint_labels", _l.ptr(r), _l.ptr(labels), _l.ptr(vol), labels.numel(), r.numel(), int(square), _st())
+    return vol
+
+
+def attn_fwd_into(qkv, out, lse, B, S, Hq, Hkv, D, causal, scale=None):
+    """attn_fwd writing into caller-owned o / lse buffers (engine path: no allocation per step)."""
+    if scale is None:
+        scale = D ** -0.5
+    base = qkv.data_ptr()
+    _l.call("vlb_attn_fwd", base, base + Hq * D * 2, base + (Hq + Hkv) * D * 2, qkv.stride(0), _l.ptr(out),
+            out.stride(0), _l.ptr(lse), B, S, Hq, Hkv, D, int(causal), float(scale), _l.cur_stream())
+    return out
