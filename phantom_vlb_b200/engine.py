@@ -215,3 +215,112 @@ class Engine:
                 ops.rmsnorm_bwd(dxn, x, L["ln1_w"], b["rstd1"], dres=dh1, out=nxt)
                 self.launches += 1
                 dx = nxt
+
+    # ------------------------------------------------------------------ full forward (backbone)
+    def backbone_forward(self, batch, save=True):
+        """batch: device tensors of the datamodule contract (src/datamodule/videollama2_vlb_datamodule.py:98-109).
+        Returns (pre-final-norm hidden [B*S, H], HRF weight mask fp32 [B, S])."""
+        cfg = self.cfg
+        vision = batch["vision"]
+        B, Tn = vision.shape[0], vision.shape[1]
+        assert Tn == cfg.num_frames and vision.dtype == torch.float32
+        assert batch["language"].shape[1] == cfg.l_text, "text length must be max_len - n_vis + 1 (litmodule.py:180-181)"
+        feats = self.vit_forward(vision.reshape(B * Tn, 3, cfg.image_size, cfg.image_size))
+        vis = self.stc_forward(feats, B)
+        ids = ops.ids_to_long(batch["language"].contiguous())
+        x0 = self.buf("L0_x", (B * cfg.max_len, cfg.hidden))
+        _, self.video_pos = ops.splice_embed(ids, self.W.llm["embed"], vis, cfg.n_vis, out=x0)
+        wm = ops.weight_mask(batch["padvals"].contiguous(), batch["vis_weights"].contiguous(),
+                             batch["lang_weights"].contiguous(), cfg.tok_per_frame, cfg.max_len)
+        self.launches += 4
+        self.vis_tokens, self.embeds = vis, x0
+        hidden = self.decoder_forward(x0, B, save=save)
+        return hidden, wm
+
+    # ------------------------------------------------------------------ brain head
+    def head_forward(self, hidden, wm, y, B, training):
+        cfg, T = self.cfg, self.T
+        H, P, S = cfg.hidden, cfg.num_target, cfg.max_len
+        nch = 64 if S >= 1024 else max(1, S // 16)
+        partial = self.buf("hd_partial", (B, nch, H), torch.float32)
+        pooled, hrf = self.buf("hd_pooled", (B, H)), self.buf("hd_hrf", (B, H))
+        drop = self.dropout_rate if training else 0.0
+        keep = self.buf("hd_keep", (B, H), torch.float32) if drop > 0 else None
+        _l.call("vlb_hrf_pool_fwd", _l.ptr(hidden), _l.ptr(self.W.llm["norm_w"]), _l.ptr(T.w("ln1_w")), _l.ptr(T.w("ln1_b")),
+                _l.ptr(wm), _l.ptr(partial), B, S, H, nch, cfg.rms_eps, cfg.head_ln_eps, _l.cur_stream())
+        self.rng_step = getattr(self, "rng_step", 0) + 1
+        _l.call("vlb_hrf_pool_finalize", _l.ptr(partial), _l.ptr(T.w("ln2_w")), _l.ptr(T.w("ln2_b")), _l.ptr(pooled),
+                _l.ptr(hrf), _l.ptr(keep), B, H, nch, cfg.head_ln_eps, float(drop), 0x5EED0000 + self.rng_step, _l.cur_stream())
+        pred = self.gemm(hrf, T.w("ridge_w"), self.buf("hd_pred", (B, P)), bias=T.w("ridge_b"))
+        acc = self.buf("hd_acc", (2,), torch.float32)
+        acc.zero_()
+        dpred = self.buf("hd_dpred", (B, P))
+        out = self.buf("hd_loss", (3,), torch.float32)
+        _l.call("vlb_head_loss", _l.ptr(pred), _l.ptr(y), _l.ptr(dpred), _l.ptr(acc), B * P, _l.cur_stream())
+        _l.call("vlb_l2_prefill", _l.ptr(T.w("ridge_w")), _l.ptr(T.g("ridge_w")), _l.ptr(acc), P * H, cfg.l2_lambda,
+                int(training), _l.cur_stream())
+        _l.call("vlb_loss_finalize", _l.ptr(acc), _l.ptr(out), B * P, cfg.l2_lambda, _l.cur_stream())
+        self.launches += 5
+        self.head_saved = dict(pooled=pooled, hrf=hrf, keep=keep, dpred=dpred, pred=pred, nch=nch)
+        return out, pred
+
+    def head_backward(self, hidden, wm, B):
+        """Gradients of ridge W/b, LN1/LN2 into T.grad; returns d(loss)/d(pre-final-norm hidden) [B*S, H] bf16."""
+        cfg, T, hs = self.cfg, self.T, self.head_saved
+        H, P, S = cfg.hidden, cfg.num_target, cfg.max_len
+        self.gemm(hs["dpred"], hs["hrf"], T.g("ridge_w"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+        _l.call("vlb_colsum", _l.ptr(hs["dpred"]), _l.ptr(T.g("ridge_b")), B, P, _l.cur_stream())
+        dhrf = self.gemm(hs["dpred"], T.w("ridge_w"), self.buf("hd_dhrf", (B, H), torch.float32), b_mn=True, out_f32=True)
+        for n in ("ln1_w", "ln1_b", "ln2_w", "ln2_b"):
+            T.g(n).zero_()
+        dpooled = self.buf("hd_dpooled", (B, H), torch.float32)
+        _l.call("vlb_ln2_bwd", _l.ptr(dhrf), _l.ptr(hs["keep"]), _l.ptr(hs["pooled"]), _l.ptr(T.w("ln2_w")), _l.ptr(dpooled),
+                _l.ptr(T.g("ln2_w")), _l.ptr(T.g("ln2_b")), B, H, cfg.head_ln_eps, _l.cur_stream())
+        dx = self.buf("bw_dx_a", (B * S, H))
+        _l.call("vlb_hrf_pool_bwd", _l.ptr(hidden), _l.ptr(self.W.llm["norm_w"]), _l.ptr(T.w("ln1_w")), _l.ptr(wm),
+                _l.ptr(dpooled), _l.ptr(dx), _l.ptr(T.g("ln1_w")), _l.ptr(T.g("ln1_b")), B, S, H, hs["nch"], cfg.rms_eps,
+                cfg.head_ln_eps, _l.cur_stream())
+        self.launches += 3
+        return dx
+
+    # ------------------------------------------------------------------ steps
+    def loss_and_grads(self, batch):
+        """One forward + backward of training_step (litmodule.py:259-306). Returns (loss[3] fp32 device tensor, pred)."""
+        B = batch["vision"].shape[0]
+        hidden, wm = self.backbone_forward(batch, save=True)
+        y = batch["timeseries"].contiguous()
+        out, pred = self.head_forward(hidden, wm, y, B, training=True)
+        dx = self.head_backward(hidden, wm, B)
+        self.decoder_backward(dx, B)
+        return out, pred
+
+    def eval_step(self, batch):
+        """validation_step (litmodule.py:309-342): loss[3], brain_preds bf16 [B,P]."""
+        B = batch["vision"].shape[0]
+        hidden, wm = self.backbone_forward(batch, save=False)
+        return self.head_forward(hidden, wm, batch["timeseries"].contiguous(), B, training=False)
+
+    def optimizer_step(self, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, max_norm=1.0, world_size=1,
+                       allreduce=None):
+        """clip_grad_norm_(max_norm) + AdamW on the flat buffer; `allreduce(tensor)` sums gradients across ranks first."""
+        T = self.T
+        if allreduce is not None:
+            allreduce(T.grad)
+        T.sumsq.zero_()
+        _l.call("vlb_grad_sumsq", _l.ptr(T.grad), T.numel, _l.ptr(T.sumsq), _l.cur_stream())
+        T.step_count += 1
+        _l.call("vlb_adamw_step", _l.ptr(T.param), _l.ptr(T.grad), _l.ptr(T.m), _l.ptr(T.v), _l.ptr(T.param_bf16), T.numel,
+                _l.ptr(T.sumsq), float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), T.step_count,
+                float(max_norm), 1.0 / world_size, _l.cur_stream())
+        T.stage_b()
+        self.launches += 2 + 7 * self.cfg.layers
+
+    def train_step(self, batch, lr, **opt):
+        out, _ = self.loss_and_grads(batch)
+        self.optimizer_step(lr, **opt)
+        return out
+
+
+def cosine_lr(base_lr, step, t_max, eta_min=0.0):
+    """torch CosineAnnealingLR closed form (litmodule.py:365-378), value used for optimiser step `step` (0-based)."""
+    return eta_min + (base_lr - eta_min) * (1 + math.cos(math.pi * step / t_max)) / 2
