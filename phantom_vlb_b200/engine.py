@@ -29,6 +29,7 @@ class Engine:
             raise NotImplementedError("lora_dropout > 0 is not implemented (parity and benchmark runs use 0)")
         self.saved = None
         self.launches = 0
+        self.profile = None
         self._bufs = {}
 
     # ------------------------------------------------------------------ buffers
@@ -43,7 +44,19 @@ class Engine:
 
     def gemm(self, a, b, out, **kw):
         self.launches += 1
-        return ops.gemm(a, b, out, **kw)
+        if self.profile is None:
+            return ops.gemm(a, b, out, **kw)
+        # instrumented pass (bench.py roofline): CUDA events around this launch + its algorithmic FLOPs
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = ops.gemm(a, b, out, **kw)
+        e1.record()
+        M, N = out.shape
+        K = a.shape[0] if kw.get("a_mn") else a.shape[1]
+        a2 = kw.get("a2")
+        K2 = 0 if a2 is None else (a2.shape[0] if kw.get("a_mn") else a2.shape[1])
+        self.profile.append((e0, e1, 2.0 * M * N * (K + K2), (M, N, K, K2)))
+        return r
 
     # ------------------------------------------------------------------ vision tower (frozen, forward only)
     def vit_forward(self, pixels):
