@@ -339,3 +339,17 @@ def glover_like(t):
     a1, a2, b = 6.0, 16.0, 1.0
     h = (t ** (a1 - 1) * np.exp(-t / b) / math.gamma(a1)) - (t ** (a2 - 1) * np.exp(-t / b) / math.gamma(a2)) / 6.0
     return h / 0.1758
+
+
+def pearson_stats(preds, target):
+    """Raw moments [5, P] (sum x, sum y, sum x^2, sum y^2, sum xy) in fp64 -- additive across row shards."""
+    x = np.nan_to_num(np.asarray(preds, dtype=np.float64))
+    y = np.nan_to_num(np.asarray(target, dtype=np.float64))
+    return np.stack([x.sum(0), y.sum(0), (x * x).sum(0), (y * y).sum(0), (x * y).sum(0)])
+
+
+def pearson_from_stats(stats, n):
+    sx, sy, sxx, syy, sxy = stats
+    with np.errstate(divide="ignore", invalid="ignore"):
+        r = (sxy - sx * sy / n) / np.sqrt((sxx - sx * sx / n) * (syy - sy * sy / n))
+    return np.clip(r, -1.0, 1.0)
