@@ -50,14 +50,12 @@ class RidgeRegressionLayer(torch.nn.Module):
 
 
 def pearson_columns(preds, targets, group=None):
-    """Per-column Pearson r on the GPU; with a process group the row shards' moments are summed first."""
+    """Per-column Pearson r on the GPU; row shards on different ranks are merged with one all-reduce of the moments."""
+    from .dp import merge_moments_
     N, P = preds.shape
     _, stats = ops.pearson(preds.contiguous(), targets.contiguous(), finalize=False)
-    n = torch.tensor([float(N)], device=preds.device, dtype=torch.float64)
-    if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
-        torch.distributed.all_reduce(stats, group=group)
-        torch.distributed.all_reduce(n, group=group)
-    return ops.pearson_finalize(stats, int(n.item()))
+    stats, n = merge_moments_(stats, N, group)
+    return ops.pearson_finalize(stats, n)
 
 
 class LogValAccuracyCallback(Callback):

@@ -1,0 +1,89 @@
+"""World-size-2 gloo tests of the data-parallel host logic (phantom_vlb_b200/dp.py): sampler sharding, the gradient
+all-reduce + 1/world folding contract of the optimiser front-end, and the Pearson moment merge.  CPU only; the CUDA
+kernels on either side of these collectives are covered by the -m gpu tests."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle.ref_model import pearson_from_stats, pearson_r, pearson_stats
+from phantom_vlb_b200 import dp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        assert dp.world() == (rank, world)
+        # ---- sampler: disjoint, equal-sized, identical permutation on every rank
+        idx = dp.shard_indices(101, rank, world, seed=1234, epoch=3)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, idx)
+        flat = sum(gathered, [])
+        assert len(set(flat)) == len(flat) == 100 and all(len(g) == 50 for g in gathered)
+        # ---- gradient exchange: sum across ranks, then grad_scale = 1/world == mean over the global batch
+        rng = np.random.RandomState(7)
+        g_all = rng.randn(world, 1000).astype(np.float32)
+        g = torch.from_numpy(g_all[rank].copy())
+        w = dp.allreduce_sum_(g)
+        assert w == world
+        assert np.allclose(g.numpy() * (1.0 / w), g_all.mean(0), atol=1e-6)
+        # global-norm clip computed AFTER the reduce is identical on all ranks -> no second collective
+        norms = [None] * world
+        dist.all_gather_object(norms, float((g * (1.0 / w)).norm()))
+        assert norms[0] == norms[1]
+        # ---- Pearson: row shards merged through the additive fp64 moments
+        x, y = rng.randn(501, 33), rng.randn(501, 33)
+        y[:, :9] += 0.5 * x[:, :9]
+        x[5, 2] = np.nan
+        rows = np.array_split(np.arange(501), world)[rank]            # ragged shards (251 / 250)
+        st = torch.from_numpy(pearson_stats(x[rows], y[rows]))
+        st, n = dp.merge_moments_(st, len(rows))
+        assert n == 501
+        r = pearson_from_stats(st.numpy(), n)
+        assert np.allclose(r, pearson_r(x, y), atol=1e-12)
+        q.put((rank, "ok"))
+    except Exception as e:                                           # pragma: no cover
+        q.put((rank, repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_dp_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], res
+
+
+def test_shard_helpers_single_process():
+    assert dp.world() == (0, 1)
+    a = dp.shard_indices(10, 0, 3, shuffle=False, drop_last=False)
+    b = dp.shard_indices(10, 1, 3, shuffle=False, drop_last=False)
+    c = dp.shard_indices(10, 2, 3, shuffle=False, drop_last=False)
+    assert len(a) == len(b) == len(c) == 4 and set(a + b + c) == set(range(10))
+    cover = []
+    for r in range(8):
+        lo, hi = dp.shard_columns(250003, r, 8)
+        assert lo % 8 == 0
+        cover += [(lo, hi)]
+    assert cover[0][0] == 0 and cover[-1][1] == 250003 and all(cover[i][1] == cover[i + 1][0] for i in range(7))
+    s = dp.ShardedSampler(20, rank=1, world_size=4, seed=1)
+    assert len(list(s)) == len(s) == 5
