@@ -26,6 +26,8 @@ void vlb_tmap_cache_clear(void);
  * C[M,N] = epi(alpha * (A·Bᵀ + A2·B2ᵀ)),  epi(v) = bf16(act(v + bias[n])) (+ residual[m,n]).
  * a_mn_major/b_mn_major = 0: operand stored [rows, K] (K contiguous); 1: stored [K, rows].
  * c_is_f32 = 1: C is fp32 [M, ldc] written (accumulate=1: added to) without rounding, bias/act/residual ignored.
+ * split_k (c_is_f32=1, accumulate=1 only): 0 = auto, 1 = off, n = contraction split n ways; partial tiles are added with
+ * red.global.add.f32, so the summation order (not the value beyond fp32 rounding) varies from run to run.
  * Replaces every nn.Linear / peft lora.Linear on the path: HF MistralDecoderLayer + LoraConfig targets
  * (src/litmodule/videollama2_vlb_litmodule.py:101-120), CLIP encoder linears (VideoLLaMA2/videollama2/model/
  * encoder.py:50), STC 1x1 convs / readout (VideoLLaMA2/videollama2/model/projector.py:153-187). */
@@ -34,7 +36,7 @@ int vlb_gemm_bf16(const void* A, int lda, const void* B, int ldb, void* C, int l
                   const void* A2, int lda2, const void* B2, int ldb2, int K2,
                   float alpha, const void* bias, const void* residual, int ldr, int act,
                   int a_mn_major, int b_mn_major, int c_is_f32, int accumulate,
-                  int block_n, int max_ctas, void* stream);
+                  int block_n, int max_ctas, int split_k, void* stream);
 
 /* ------------------------------------------------------------------ flash attention (tcgen05, TMEM-resident S/O)
  * q/k/v point into a fused projection buffer with row stride ld_qkv: q [B*S, Hq*D], k/v [B*S, Hkv*D].

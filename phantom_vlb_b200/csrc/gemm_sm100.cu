@@ -50,6 +50,7 @@ struct GemmParams {
     float* c_f32;           // when non-null: fp32 output [M, ldc32] written straight from registers (gradients)
     int ldc32;
     int accum_f32;          // c_f32 += result instead of =
+    int splits;             // split-K factor (fp32 accumulate outputs only): partial tiles are red.add'ed
 };
 
 __device__ __forceinline__ void tile_coords(int t, int mt, int nt, int& mb, int& nb) {
@@ -61,6 +62,14 @@ __device__ __forceinline__ void tile_coords(int t, int mt, int nt, int& mb, int&
     const int r = t - g * per_group;
     mb = first_m + (r % gm);
     nb = r / gm;
+}
+
+// work item t -> (output tile, k-block range) when the contraction is split `splits` ways
+__device__ __forceinline__ void split_range(int t, int splits, int nk, int& tile, int& kb0, int& kb1) {
+    tile = t / splits;
+    const int s = t - tile * splits;
+    kb0 = (int)((long long)nk * s / splits);
+    kb1 = (int)((long long)nk * (s + 1) / splits);
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -86,7 +95,7 @@ gemm_tcgen05_kernel(const GemmParams p,
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int nk = p.nk1 + p.nk2;
-    const int num_tiles = p.mt * p.nt;
+    const int num_tiles = p.mt * p.nt * p.splits;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA1); tma_prefetch_desc(&tmB1); tma_prefetch_desc(&tmC);
@@ -108,9 +117,10 @@ gemm_tcgen05_kernel(const GemmParams p,
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                int mb, nb; tile_coords(t, p.mt, p.nt, mb, nb);
+                int tile, kb0, kb1; split_range(t, p.splits, nk, tile, kb0, kb1);
+                int mb, nb; tile_coords(tile, p.mt, p.nt, mb, nb);
                 const int m0 = mb * BM, n0 = nb * BN;
-                for (int kb = 0; kb < nk; ++kb) {
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
                     const bool second = kb >= p.nk1;
@@ -153,7 +163,8 @@ gemm_tcgen05_kernel(const GemmParams p,
                 mbar_wait(&tempty_bar[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
-                for (int kb = 0; kb < nk; ++kb) {
+                int tile, kb0, kb1; split_range(t, p.splits, nk, tile, kb0, kb1);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_BYTES);
@@ -162,10 +173,10 @@ gemm_tcgen05_kernel(const GemmParams p,
                     for (int k = 0; k < BK / 16; ++k) {
                         const uint64_t ad = make_smem_desc(a_addr + k * KSTEP_A, A_MN ? LBO : 0, 1024);
                         const uint64_t bd = make_smem_desc(b_addr + k * KSTEP_B, B_MN ? LBO : 0, 1024);
-                        umma_bf16(d_tmem, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[stage]);                 // frees this smem stage when the MMAs retire
-                    if (kb == nk - 1) umma_commit(&tfull_bar[as]);  // accumulator ready for the epilogue
+                    if (kb == kb1 - 1) umma_commit(&tfull_bar[as]);  // accumulator ready for the epilogue
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -178,7 +189,7 @@ gemm_tcgen05_kernel(const GemmParams p,
         uint32_t cd_idx = 0;
         const bool issuer = (warp == 4 && lane == 0);
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-            int mb, nb; tile_coords(t, p.mt, p.nt, mb, nb);
+            int mb, nb; tile_coords(t / p.splits, p.mt, p.nt, mb, nb);
             const int m0 = mb * BM, n0 = nb * BN;
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
@@ -200,6 +211,10 @@ gemm_tcgen05_kernel(const GemmParams p,
                             if (n0 + c0 + c * 4 < p.N) {      // N is a multiple of 8
                                 float4 v = make_float4(__uint_as_float(r[c * 4]) * p.alpha, __uint_as_float(r[c * 4 + 1]) * p.alpha,
                                                        __uint_as_float(r[c * 4 + 2]) * p.alpha, __uint_as_float(r[c * 4 + 3]) * p.alpha);
+                                if (p.splits > 1) {
+                                    atomicAdd(reinterpret_cast<float4*>(dst + c * 4), v);     // red.global.add.v4.f32
+                                    continue;
+                                }
                                 if (p.accum_f32) {
                                     const float4 o = *reinterpret_cast<const float4*>(dst + c * 4);
                                     v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
@@ -372,6 +387,7 @@ struct GemmArgs {
     const void* bias; const void* residual; int ldr; int act;
     int a_mn, b_mn;     // operand storage: 0 = [rows, K] (K-major), 1 = [K, rows] (MN-major)
     int max_ctas;       // 0 = all SMs
+    int split_k;        // 0 = auto (fp32 accumulate outputs only), 1 = off, >1 = forced
 };
 
 template <int BN, bool A_MN, bool B_MN>
@@ -408,6 +424,16 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     p.mt = ceil_div(a.M, BM); p.nt = ceil_div(a.N, BN);
     p.c_f32 = a.c_is_f32 ? reinterpret_cast<float*>(a.C) : nullptr;
     p.ldc32 = a.ldc; p.accum_f32 = a.accum;
+    // split-K: gradient GEMMs contract over all tokens into a tiny [r, N] output; without it only mt*nt (< 148) CTAs
+    // stream the activations. Partial tiles are red.add'ed, so the output must already hold the value to add to.
+    p.splits = 1;
+    if (a.c_is_f32 && a.accum && a.split_k != 1) {
+        const int nk = p.nk1 + p.nk2;
+        int sp = a.split_k > 1 ? a.split_k : num_sms() / (p.mt * p.nt);
+        if (sp > nk / 4) sp = nk / 4;          // keep >= 4 k-blocks (256 contraction rows) per partial tile
+        if (sp > 1) p.splits = sp;
+    }
+    VLB_REQUIRE(a.split_k <= 1 || (a.c_is_f32 && a.accum), "gemm: split_k=%d needs c_is_f32=1 and accumulate=1", a.split_k);
 
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
     static bool attr_set = false;
@@ -416,7 +442,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
         VLB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(gemm smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
         attr_set = true;
     }
-    int grid = p.mt * p.nt;
+    int grid = p.mt * p.nt * p.splits;
     int cap = a.max_ctas > 0 ? a.max_ctas : num_sms();
     if (grid > cap) grid = cap;
     kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC);
@@ -457,13 +483,13 @@ extern "C" int vlb_gemm_bf16(const void* A, int lda, const void* B, int ldb, voi
                              const void* A2, int lda2, const void* B2, int ldb2, int K2,
                              float alpha, const void* bias, const void* residual, int ldr, int act,
                              int a_mn_major, int b_mn_major, int c_is_f32, int accumulate,
-                             int block_n, int max_ctas, void* stream) {
+                             int block_n, int max_ctas, int split_k, void* stream) {
     vlb::GemmArgs a;
     a.A1 = A; a.lda1 = lda; a.K1 = K; a.B1 = B; a.ldb1 = ldb;
     a.A2 = A2; a.lda2 = lda2; a.K2 = (A2 && B2) ? K2 : 0; a.B2 = B2; a.ldb2 = ldb2;
     a.C = C; a.ldc = ldc; a.c_is_f32 = c_is_f32; a.accum = accumulate; a.M = M; a.N = N; a.alpha = alpha;
     a.bias = bias; a.residual = residual; a.ldr = ldr; a.act = act;
-    a.a_mn = a_mn_major; a.b_mn = b_mn_major; a.max_ctas = max_ctas;
+    a.a_mn = a_mn_major; a.b_mn = b_mn_major; a.max_ctas = max_ctas; a.split_k = split_k;
     return vlb::gemm_dispatch(a, block_n, reinterpret_cast<cudaStream_t>(stream));
 }
 

@@ -195,21 +195,21 @@ class Engine:
             # ---- down_proj: x_next = h1 + act Wd^T + s (act A_d^T) B_d^T
             self.gemm(dx, bc["d"], t16, b_mn=True, alpha=s)
             self.gemm(dx, L["wd"], dact, a2=t16, b2=T.w(p + "A_d"), b_mn=True)
-            self.gemm(t16, b["act"], T.g(p + "A_d"), a_mn=True, b_mn=True, out_f32=True)
-            self.gemm(b["xa4"], dx, T.g(p + "Bt_d"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(t16, b["act"], T.g(p + "A_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(b["xa4"], dx, T.g(p + "Bt_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             ops.swiglu_bwd(b["gu"], dact, out=dgu)
             # ---- gate/up
             self.gemm(dgu, bc["gu"], t32, b_mn=True, alpha=s)
             self.gemm(dgu, L["wgu"], dxn, a2=t32, b2=T.w(p + "Acat_gu"), b_mn=True)
-            self.gemm(t32, b["xn2"], T.g(p + "Acat_gu"), a_mn=True, b_mn=True, out_f32=True)
-            self.gemm(b["xa3"][:, 0:r], dgu[:, 0:I], T.g(p + "Bt_g"), a_mn=True, b_mn=True, out_f32=True)
-            self.gemm(b["xa3"][:, r:2 * r], dgu[:, I:2 * I], T.g(p + "Bt_u"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(t32, b["xn2"], T.g(p + "Acat_gu"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(b["xa3"][:, 0:r], dgu[:, 0:I], T.g(p + "Bt_g"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(b["xa3"][:, r:2 * r], dgu[:, I:2 * I], T.g(p + "Bt_u"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             ops.rmsnorm_bwd(dxn, b["h1"], L["ln2_w"], b["rstd2"], dres=dx, out=dh1)
             # ---- o_proj: h1 = x + o Wo^T + s (o A_o^T) B_o^T
             self.gemm(dh1, bc["o"], t16, b_mn=True, alpha=s)
             self.gemm(dh1, L["wo"], do, a2=t16, b2=T.w(p + "A_o"), b_mn=True)
-            self.gemm(t16, b["o"], T.g(p + "A_o"), a_mn=True, b_mn=True, out_f32=True)
-            self.gemm(b["xa2"], dh1, T.g(p + "Bt_o"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(t16, b["o"], T.g(p + "A_o"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(b["xa2"], dh1, T.g(p + "Bt_o"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             # ---- attention + RoPE
             ops.attn_bwd(b["qkv"], b["o"], do, b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True, dqkv=dqkv, dq_f32=dq32,
                          delta=delta)
@@ -217,10 +217,10 @@ class Engine:
             ops.rope_(dqkv[:, nq:], W.llm["cos"], W.llm["sin"], S, cfg.kv_heads, D, inverse=True)
             # ---- q/k/v
             self.gemm(dqkv, bc["qkv"], t48, b_mn=True, alpha=s)
-            self.gemm(t48, b["xn1"], T.g(p + "Acat_qkv"), a_mn=True, b_mn=True, out_f32=True)
-            self.gemm(b["xa1"][:, 0:r], dqkv[:, 0:nq], T.g(p + "Bt_q"), a_mn=True, b_mn=True, out_f32=True)
-            self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True)
-            self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True)
+            self.gemm(t48, b["xn1"], T.g(p + "Acat_qkv"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(b["xa1"][:, 0:r], dqkv[:, 0:nq], T.g(p + "Bt_q"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.launches += 7
             if l > 0:        # the spliced embeddings are frozen: layer 0 needs no input gradient
                 self.gemm(dqkv, L["wqkv"], dxn, a2=t48, b2=T.w(p + "Acat_qkv"), b_mn=True)
@@ -284,8 +284,6 @@ class Engine:
         self.gemm(hs["dpred"], hs["hrf"], T.g("ridge_w"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
         _l.call("vlb_colsum", _l.ptr(hs["dpred"]), _l.ptr(T.g("ridge_b")), B, P, _l.cur_stream())
         dhrf = self.gemm(hs["dpred"], T.w("ridge_w"), self.buf("hd_dhrf", (B, H), torch.float32), b_mn=True, out_f32=True)
-        for n in ("ln1_w", "ln1_b", "ln2_w", "ln2_b"):
-            T.g(n).zero_()
         dpooled = self.buf("hd_dpooled", (B, H), torch.float32)
         _l.call("vlb_ln2_bwd", _l.ptr(dhrf), _l.ptr(hs["keep"]), _l.ptr(hs["pooled"]), _l.ptr(T.w("ln2_w")), _l.ptr(dpooled),
                 _l.ptr(T.g("ln2_w")), _l.ptr(T.g("ln2_b")), B, H, cfg.head_ln_eps, _l.cur_stream())
@@ -300,6 +298,7 @@ class Engine:
     def loss_and_grads(self, batch):
         """One forward + backward of training_step (litmodule.py:259-306). Returns (loss[3] fp32 device tensor, pred)."""
         B = batch["vision"].shape[0]
+        self.T.grad.zero_()      # every gradient kernel below ACCUMULATES (split-K red.add GEMMs, LN atomics)
         hidden, wm = self.backbone_forward(batch, save=True)
         y = batch["timeseries"].contiguous()
         out, pred = self.head_forward(hidden, wm, y, B, training=True)

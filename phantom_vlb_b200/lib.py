@@ -69,8 +69,33 @@ def last_error():
     return lib().vlb_last_error_string().decode("utf-8", "replace")
 
 
+_prof = None       # when a list: (name, start_event, end_event, args) per call (tools/breakdown.py, bench.py roofline pass)
+
+
+def profile_begin():
+    global _prof
+    _prof = []
+
+
+def profile_end():
+    """-> [(name, milliseconds, args)] for every call since profile_begin() (synchronises the device)."""
+    global _prof
+    import torch
+    torch.cuda.synchronize()
+    rows, _prof = _prof, None
+    return [(n, e0.elapsed_time(e1), a) for n, e0, e1, a in rows]
+
+
 def call(name, *args):
-    rc = getattr(lib(), name)(*args)
+    if _prof is not None and name != "vlb_check_device":
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = getattr(lib(), name)(*args)
+        e1.record()
+        _prof.append((name, e0, e1, args))
+    else:
+        rc = getattr(lib(), name)(*args)
     if rc != 0:
         raise RuntimeError("%s failed (%d): %s" % (name, rc, last_error()))
 

@@ -14,7 +14,7 @@ def _chk(t, dtype=None):
 
 
 def gemm(a, b, out=None, *, a2=None, b2=None, alpha=1.0, bias=None, residual=None, act=ACT_NONE,
-         a_mn=False, b_mn=False, out_f32=False, accumulate=False, block_n=0, max_ctas=0):
+         a_mn=False, b_mn=False, out_f32=False, accumulate=False, block_n=0, max_ctas=0, split_k=0):
     """out[M,N] = epi(alpha * (a @ b.T + a2 @ b2.T)).
 
     a: [M,K] (a_mn: stored [K,M]); b: [N,K] (b_mn: stored [K,N]); a2/b2 likewise with their own K2 (LoRA block).
@@ -43,7 +43,7 @@ def gemm(a, b, out=None, *, a2=None, b2=None, alpha=1.0, bias=None, residual=Non
             M, N, K,
             _l.ptr(a2), a2.stride(0) if a2 is not None else 0, _l.ptr(b2), b2.stride(0) if b2 is not None else 0, K2,
             float(alpha), _l.ptr(bias), _l.ptr(residual), residual.stride(0) if residual is not None else 0, int(act),
-            int(a_mn), int(b_mn), int(out_f32), int(accumulate), int(block_n), int(max_ctas), _l.cur_stream())
+            int(a_mn), int(b_mn), int(out_f32), int(accumulate), int(block_n), int(max_ctas), int(split_k), _l.cur_stream())
     return out
 
 

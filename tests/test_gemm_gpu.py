@@ -88,3 +88,27 @@ def test_gemm_persistent_many_tiles():
     out = ops.gemm(a, b)
     torch.cuda.synchronize()
     _close(out, a.float() @ b.float().t())
+
+
+@pytest.mark.parametrize("M,N,K,split", [(16, 4096, 8192, 0), (48, 4096, 8192, 0), (16, 14336, 4096 + 64, 7), (32, 1000, 3 * 64, 0),
+                                         (16, 4096, 8192, 1)])
+def test_gemm_split_k_red_add(M, N, K, split):
+    """LoRA-gradient shape: tiny [r, N] fp32 output, contraction over all tokens split across CTAs with red.add."""
+    from phantom_vlb_b200 import ops
+    torch.manual_seed(2)
+    a = (torch.randn(K, M, device="cuda") * 0.1).bfloat16()
+    b = (torch.randn(K, N, device="cuda") * 0.1).bfloat16()
+    base = torch.randn(M, N, device="cuda", dtype=torch.float32)
+    out = base.clone()
+    ops.gemm(a, b, out, a_mn=True, b_mn=True, out_f32=True, accumulate=True, alpha=0.5, split_k=split)
+    torch.cuda.synchronize()
+    ref = base + 0.5 * (a.float().t() @ b.float())
+    _close(out, ref, 1e-4)
+
+
+def test_gemm_split_k_needs_accumulate():
+    from phantom_vlb_b200 import ops
+    a = torch.zeros(256, 16, device="cuda").bfloat16()
+    b = torch.zeros(256, 128, device="cuda").bfloat16()
+    with pytest.raises(RuntimeError):
+        ops.gemm(a, b, a_mn=True, b_mn=True, out_f32=True, accumulate=False, split_k=4)
