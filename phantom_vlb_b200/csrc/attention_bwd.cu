@@ -11,16 +11,26 @@
 //   threads : P^T = exp2(S^T*c - LSE), dS^T = P^T o (dP^T - Delta)  -> bf16 -> swizzled smem
 //   (3) dV_j += P^T dO_i          (4) dK_j += dS^T Q_i            [M128 N128 K64]  accumulate in TMEM over the sweep
 //   (5) dQ_i^T = K_j^T dS^T       [M128(d) N64(q) K128(keys)]  -> TMEM -> fp32 red.global (coalesced along d)
-// warp 0 TMA producer (Q_i, dO_i, LSE_i, Delta_i through a 2-stage ring), warp 1 MMA issuer, warp 2 TMEM allocator,
-// warps 4-7 softmax / dQ reduction / epilogue.
+//
+// Software pipeline (r01b): the tensor pipe and the softmax threads never wait on each other's full step.
+//   * S^T is double-buffered in TMEM and issued TWO steps ahead, dP^T one step ahead, so while the 8 softmax warps
+//     work on step t the tensor core runs dP(t+1), dV/dK/dQ(t-1..t) and S(t+2);
+//   * P^T / dS^T are double-buffered in shared memory, Q/dO/LSE/Delta ride a 3-stage TMA ring;
+//   * the softmax side is two warpgroups splitting the 64 query columns (a warp can only reach its own 32 TMEM lanes,
+//     so the split has to be along columns); the dQ^T drain of step t-1 happens after step t's P/dS hand-off.
+// TMEM: S0 | S1 | dP | dQ (64 columns each) | dV | dK (128 each) = 512 columns.
+// warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4-11 softmax / dQ reduction / epilogue.
 #include "common.cuh"
+
+#include <stdlib.h>
 
 namespace vlb {
 
 constexpr int BW_D = 128;
 constexpr int BW_BK = 128;      // keys per CTA
 constexpr int BW_BQ = 64;       // query rows per inner step
-constexpr int BW_THREADS = 256;
+constexpr int BW_NST = 3;       // Q/dO ring stages
+constexpr int BW_THREADS = 384;
 
 struct BwCfg {
     static constexpr int KV_BYTES = BW_BK * BW_D * 2;          // 32 KB each
@@ -28,16 +38,17 @@ struct BwCfg {
     static constexpr int PS_BYTES = BW_BK * BW_BQ * 2;         // 16 KB each
     static constexpr int OFF_K = 0;
     static constexpr int OFF_V = KV_BYTES;
-    static constexpr int OFF_Q = 2 * KV_BYTES;                 // [2 stages]
-    static constexpr int OFF_DO = OFF_Q + 2 * QDO_BYTES;       // [2 stages]
-    static constexpr int OFF_P = OFF_DO + 2 * QDO_BYTES;
-    static constexpr int OFF_DS = OFF_P + PS_BYTES;
-    static constexpr int OFF_VEC = OFF_DS + PS_BYTES;          // [2 stages][lse 64 | delta 64] floats
-    static constexpr int OFF_BAR = OFF_VEC + 2 * 2 * BW_BQ * 4;
-    static constexpr int SMEM_BYTES = OFF_BAR + 128;
-    static constexpr int T_S = 0, T_DP = 64, T_DQ = 128, T_DV = 192, T_DK = 320;   // TMEM columns
+    static constexpr int OFF_Q = 2 * KV_BYTES;                         // [3 stages]
+    static constexpr int OFF_DO = OFF_Q + BW_NST * QDO_BYTES;          // [3 stages]
+    static constexpr int OFF_P = OFF_DO + BW_NST * QDO_BYTES;          // [2 buffers]
+    static constexpr int OFF_DS = OFF_P + 2 * PS_BYTES;                // [2 buffers]
+    static constexpr int OFF_VEC = OFF_DS + 2 * PS_BYTES;              // [3 stages][lse 64 | delta 64] floats
+    static constexpr int OFF_BAR = OFF_VEC + BW_NST * 2 * BW_BQ * 4;
+    static constexpr int SMEM_BYTES = OFF_BAR + 256;
+    static constexpr int T_S = 0, T_DP = 128, T_DQ = 192, T_DV = 256, T_DK = 384;   // TMEM columns (S: two 64-col buffers)
     static constexpr int TMEM_COLS = 512;
 };
+static_assert(BwCfg::SMEM_BYTES <= 232448, "attention backward shared memory exceeds the 227 KB per-CTA limit");
 
 struct BwParams {
     int S, Hq, Hkv, group, causal;
@@ -47,6 +58,8 @@ struct BwParams {
     float* dq;              // [B*S, Hq*D] fp32, pre-zeroed
     bf16* dk; bf16* dv;     // rows [B*S], row stride ld_dkv, head hk at column hk*D
     int ld_dkv;
+    int nkb, nbh;           // key blocks per sequence, Hkv * B
+    int dbg;                // VLB_BW_DBG timing experiments (bit0: skip dQ reduction, bit1: skip exp2) -- never set in product runs
 };
 
 __global__ void __launch_bounds__(BW_THREADS, 1)
@@ -63,17 +76,20 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
     uint8_t* sDS = smem + Cfg::OFF_DS;
     float* sVec = reinterpret_cast<float*>(smem + Cfg::OFF_VEC);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
-    uint64_t* kv_full = bars;           // [1]
-    uint64_t* qdo_full = bars + 1;      // [2]
-    uint64_t* qdo_empty = bars + 3;     // [2]
-    uint64_t* s_full = bars + 5;        // S^T and dP^T ready
-    uint64_t* pds_ready = bars + 6;     // count 128: P^T, dS^T in smem; S/dP TMEM drained
-    uint64_t* mma_done = bars + 7;      // (3)(4)(5) of a step retired: smem P/dS free, dQ^T readable
-    uint64_t* dq_free = bars + 8;       // count 128: dQ^T TMEM drained
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
+    uint64_t* kv_full = bars;            // [1]
+    uint64_t* qdo_full = bars + 1;       // [3]
+    uint64_t* qdo_empty = bars + 4;      // [3]
+    uint64_t* s_full = bars + 7;         // [2] S^T buffer (t & 1) ready
+    uint64_t* dp_full = bars + 9;        // dP^T(t) ready
+    uint64_t* pds_ready = bars + 10;     // count 256: P^T, dS^T(t) in smem; S(t) / dP(t) TMEM drained
+    uint64_t* mma_done = bars + 11;      // (3)(4)(5) of a step retired: smem P/dS buffer free, dQ^T readable
+    uint64_t* dq_free = bars + 12;       // count 256: dQ^T TMEM drained
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int j = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
+    // heaviest key blocks (j = 0 sees every query block) are dispatched first
+    const int j = blockIdx.x / p.nbh;
+    const int hk = (blockIdx.x % p.nbh) % p.Hkv, b = (blockIdx.x % p.nbh) / p.Hkv;
     const int k0 = j * BW_BK;
     const int nq = p.S / BW_BQ;
     const int i_start = p.causal ? (k0 / BW_BQ) : 0;
@@ -85,8 +101,9 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
     }
     if (warp == 1 && lane == 0) {
         mbar_init(kv_full, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1); }
-        mbar_init(s_full, 1); mbar_init(pds_ready, 128); mbar_init(mma_done, 1); mbar_init(dq_free, 128);
+        for (int i = 0; i < BW_NST; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1); }
+        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(dp_full, 1);
+        mbar_init(pds_ready, 256); mbar_init(mma_done, 1); mbar_init(dq_free, 256);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
@@ -103,8 +120,8 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 tma_load_3d(&tmK, kv_full, sK + c * (BW_BK * 128), hk * BW_D + c * 64, k0, b);
                 tma_load_3d(&tmV, kv_full, sV + c * (BW_BK * 128), hk * BW_D + c * 64, k0, b);
             }
+            int st = 0; uint32_t ph = 0;
             for (int t = 0; t < T; ++t) {
-                const int st = t & 1; const uint32_t ph = (t >> 1) & 1;
                 const int h = hk * p.group + t / per_head;
                 const int q0 = (i_start + t % per_head) * BW_BQ;
                 mbar_wait(&qdo_empty[st], ph ^ 1);
@@ -117,6 +134,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 const size_t voff = ((size_t)b * p.Hq + h) * p.S + q0;
                 bulk_load_1d(sVec + st * 2 * BW_BQ, p.lse + voff, BW_BQ * 4, &qdo_full[st]);
                 bulk_load_1d(sVec + st * 2 * BW_BQ + BW_BQ, p.delta + voff, BW_BQ * 4, &qdo_full[st]);
+                if (++st == BW_NST) { st = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -124,21 +142,23 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
             constexpr uint32_t id_s = make_idesc_bf16(128, BW_BQ, false, false);    // (1)(2): A,B K-major
             constexpr uint32_t id_acc = make_idesc_bf16(128, BW_D, false, true);    // (3)(4): A K-major, B MN-major
             constexpr uint32_t id_dq = make_idesc_bf16(128, BW_BQ, true, true);     // (5): A,B MN-major
-            const uint32_t ka = smem_u32(sK), va = smem_u32(sV), pa = smem_u32(sP), dsa = smem_u32(sDS);
-            mbar_wait(kv_full, 0);
-            for (int t = 0; t < T; ++t) {
-                const int st = t & 1;
-                mbar_wait(&qdo_full[st], (t >> 1) & 1);
+            const uint32_t ka = smem_u32(sK), va = smem_u32(sV);
+            auto issue_s = [&](int t) {            // (1) S^T(t) -> S buffer t & 1 ; waits for the Q/dO stage of step t
+                const int st = t % BW_NST;
+                mbar_wait(&qdo_full[st], (t / BW_NST) & 1);
                 tc_fence_after();
-                const uint32_t qa = smem_u32(sQ + st * Cfg::QDO_BYTES), doa = smem_u32(sDO + st * Cfg::QDO_BYTES);
-                // S/dP TMEM columns were drained before pds_ready(t-1), which this thread waited on in step t-1
+                const uint32_t qa = smem_u32(sQ + st * Cfg::QDO_BYTES);
 #pragma unroll
                 for (int k = 0; k < BW_D / 16; ++k) {
                     const uint32_t offA = (k >> 2) * (BW_BK * 128) + (k & 3) * 32;
                     const uint32_t offB = (k >> 2) * (BW_BQ * 128) + (k & 3) * 32;
-                    umma_bf16(tmem_base + Cfg::T_S, make_smem_desc(ka + offA, 0, 1024), make_smem_desc(qa + offB, 0, 1024),
-                              id_s, k > 0 ? 1u : 0u);
+                    umma_bf16(tmem_base + Cfg::T_S + (t & 1) * BW_BQ, make_smem_desc(ka + offA, 0, 1024),
+                              make_smem_desc(qa + offB, 0, 1024), id_s, k > 0 ? 1u : 0u);
                 }
+                umma_commit(&s_full[t & 1]);
+            };
+            auto issue_dp = [&](int t) {           // (2) dP^T(t); the stage was already waited for by issue_s(t)
+                const uint32_t doa = smem_u32(sDO + (t % BW_NST) * Cfg::QDO_BYTES);
 #pragma unroll
                 for (int k = 0; k < BW_D / 16; ++k) {
                     const uint32_t offA = (k >> 2) * (BW_BK * 128) + (k & 3) * 32;
@@ -146,9 +166,19 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                     umma_bf16(tmem_base + Cfg::T_DP, make_smem_desc(va + offA, 0, 1024), make_smem_desc(doa + offB, 0, 1024),
                               id_s, k > 0 ? 1u : 0u);
                 }
-                umma_commit(s_full);
-                mbar_wait(pds_ready, t & 1);
+                umma_commit(dp_full);
+            };
+            mbar_wait(kv_full, 0);
+            issue_s(0);
+            issue_dp(0);
+            if (T > 1) issue_s(1);
+            for (int t = 0; t < T; ++t) {
+                const int st = t % BW_NST;
+                const uint32_t qa = smem_u32(sQ + st * Cfg::QDO_BYTES), doa = smem_u32(sDO + st * Cfg::QDO_BYTES);
+                const uint32_t pa = smem_u32(sP + (t & 1) * Cfg::PS_BYTES), dsa = smem_u32(sDS + (t & 1) * Cfg::PS_BYTES);
+                mbar_wait(pds_ready, t & 1);       // P/dS(t) in smem; S(t), dP(t) TMEM columns drained
                 tc_fence_after();
+                if (t + 1 < T) issue_dp(t + 1);
 #pragma unroll
                 for (int k = 0; k < BW_BQ / 16; ++k) {          // (3) dV += P^T dO ; (4) dK += dS^T Q
                     umma_bf16(tmem_base + Cfg::T_DV, make_smem_desc(pa + k * 32, 0, 1024),
@@ -164,80 +194,94 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 }
                 umma_commit(&qdo_empty[st]);
                 umma_commit(mma_done);
+                if (t + 2 < T) issue_s(t + 2);     // S buffer t & 1 was drained before pds_ready(t)
             }
         }
     } else if (warp >= 4) {
-        const int qd = warp & 3;
+        const int qd = warp & 3;                         // TMEM lane quadrant this warp may touch
+        const int wg = (warp - 4) >> 2;                  // which 32 of the 64 query columns
         const int row = qd * 32 + lane;                  // key row (steps 1-4) / d index (step 5)
         const uint32_t tb = tmem_base + ((uint32_t)(qd * 32) << 16);
         const int key = k0 + row;
+        const int cb = wg * 32;
         auto drain_dq = [&](int t) {
             const int h = hk * p.group + t / per_head;
             const int q0 = (i_start + t % per_head) * BW_BQ;
-            float* dst = p.dq + ((size_t)b * p.S + q0) * ((size_t)p.Hq * BW_D) + (size_t)h * BW_D + row;
-#pragma unroll 1
-            for (int c0 = 0; c0 < BW_BQ; c0 += 32) {
-                uint32_t r[32];
-                tmem_ld32(tb + Cfg::T_DQ + c0, r);
-                tmem_ld_wait();
+            float* dst = p.dq + ((size_t)b * p.S + q0 + cb) * ((size_t)p.Hq * BW_D) + (size_t)h * BW_D + row;
+            uint32_t r[32];
+            tmem_ld32(tb + Cfg::T_DQ + cb, r);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(dq_free);                        // registers hold the tile: the next dQ^T MMA may overwrite TMEM
+            if (!(p.dbg & 1)) {
 #pragma unroll
                 for (int c = 0; c < 32; ++c)
-                    atomicAdd(dst + (size_t)(c0 + c) * ((size_t)p.Hq * BW_D), __uint_as_float(r[c]) * p.scale);
+                    atomicAdd(dst + (size_t)c * ((size_t)p.Hq * BW_D), __uint_as_float(r[c]) * p.scale);
             }
         };
         for (int t = 0; t < T; ++t) {
-            const int st = t & 1;
+            const int st = t % BW_NST;
             const int q0 = (i_start + t % per_head) * BW_BQ;
-            mbar_wait(&qdo_full[st], (t >> 1) & 1);      // lse/delta vectors landed (bulk copies on the same barrier)
-            mbar_wait(s_full, t & 1);
-            tc_fence_after();
-            const float* lse = sVec + st * 2 * BW_BQ;
+            mbar_wait(&qdo_full[st], (t / BW_NST) & 1);  // lse/delta vectors landed (bulk copies on the same barrier)
+            const float* lse = sVec + st * 2 * BW_BQ + cb;
             const float* dl = lse + BW_BQ;
             const bool diag = p.causal && (q0 < k0 + BW_BK);      // some (key > query) pairs in this tile
-            if (t > 0) mbar_wait(mma_done, (t - 1) & 1);          // smem P/dS free again; dQ^T(t-1) complete
-#pragma unroll 1
-            for (int half = 0; half < 2; ++half) {
-                uint32_t rs[32], rp[32];
-                tmem_ld32(tb + Cfg::T_S + half * 32, rs);
-                tmem_ld32(tb + Cfg::T_DP + half * 32, rp);
+            uint8_t* pP = sP + (t & 1) * Cfg::PS_BYTES + row * 128;
+            uint8_t* pDS = sDS + (t & 1) * Cfg::PS_BYTES + row * 128;
+            float pv[32];
+            {   // phase A: P^T = exp2(S^T * c - LSE) for this thread's key row and 32 query columns
+                uint32_t rs[32];
+                mbar_wait(&s_full[t & 1], (t >> 1) & 1);
+                tc_fence_after();
+                tmem_ld32(tb + Cfg::T_S + (t & 1) * BW_BQ + cb, rs);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    float pe = (p.dbg & 2) ? __uint_as_float(rs[c]) : exp2f(__uint_as_float(rs[c]) * p.scale_log2 - lse[c]);
+                    if (diag && key > q0 + cb + c) pe = 0.f;
+                    pv[c] = pe;
+                }
+#pragma unroll
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    uint4 u;
+                    u.x = pack_bf16(pv[c8 * 8 + 0], pv[c8 * 8 + 1]); u.y = pack_bf16(pv[c8 * 8 + 2], pv[c8 * 8 + 3]);
+                    u.z = pack_bf16(pv[c8 * 8 + 4], pv[c8 * 8 + 5]); u.w = pack_bf16(pv[c8 * 8 + 6], pv[c8 * 8 + 7]);
+                    *reinterpret_cast<uint4*>(pP + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;
+                }
+            }
+            {   // phase B: dS^T = P^T o (dP^T - Delta)
+                uint32_t rp[32];
+                mbar_wait(dp_full, t & 1);
+                tc_fence_after();
+                tmem_ld32(tb + Cfg::T_DP + cb, rp);
                 tmem_ld_wait();
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
-                    float pv[8], dsv[8];
+                    float d[8];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const int c = half * 32 + c8 * 8 + e;
-                        float pe = exp2f(__uint_as_float(rs[c8 * 8 + e]) * p.scale_log2 - lse[c]);
-                        if (diag && key > q0 + c) pe = 0.f;
-                        pv[e] = pe;
-                        dsv[e] = pe * (__uint_as_float(rp[c8 * 8 + e]) - dl[c]);
-                    }
-                    uint4 up, ud;
-                    up.x = pack_bf16(pv[0], pv[1]); up.y = pack_bf16(pv[2], pv[3]); up.z = pack_bf16(pv[4], pv[5]); up.w = pack_bf16(pv[6], pv[7]);
-                    ud.x = pack_bf16(dsv[0], dsv[1]); ud.y = pack_bf16(dsv[2], dsv[3]); ud.z = pack_bf16(dsv[4], dsv[5]); ud.w = pack_bf16(dsv[6], dsv[7]);
-                    const int chunk = half * 4 + c8;
-                    const int off = row * 128 + ((chunk ^ (row & 7)) << 4);
-                    *reinterpret_cast<uint4*>(sP + off) = up;
-                    *reinterpret_cast<uint4*>(sDS + off) = ud;
+                    for (int e = 0; e < 8; ++e) d[e] = pv[c8 * 8 + e] * (__uint_as_float(rp[c8 * 8 + e]) - dl[c8 * 8 + e]);
+                    uint4 u;
+                    u.x = pack_bf16(d[0], d[1]); u.y = pack_bf16(d[2], d[3]); u.z = pack_bf16(d[4], d[5]); u.w = pack_bf16(d[6], d[7]);
+                    *reinterpret_cast<uint4*>(pDS + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;
                 }
             }
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(pds_ready);
             if (t > 0) {
+                mbar_wait(mma_done, (t - 1) & 1);        // dQ^T(t-1) complete; P/dS buffer (t-1)&1 free for step t+1
+                tc_fence_after();
                 drain_dq(t - 1);
-                tc_fence_before();
-                mbar_arrive(dq_free);
             }
         }
         mbar_wait(mma_done, (T - 1) & 1);
         tc_fence_after();
         drain_dq(T - 1);
-        // ---- epilogue: dV_j, dK_j (x softmax scale) -> bf16 -> global rows [b*S + key], head hk
+        // ---- epilogue: dV_j, dK_j (x softmax scale) -> bf16 -> global rows [b*S + key], head hk; each warpgroup 64 columns
         bf16* dvr = p.dv + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
         bf16* dkr = p.dk + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BW_D; c0 += 32) {
+        for (int c0 = wg * 64; c0 < wg * 64 + 64; c0 += 32) {
             uint32_t r[32];
             tmem_ld32(tb + Cfg::T_DV + c0, r);
             tmem_ld_wait();
@@ -323,13 +367,15 @@ extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_
     p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
     p.lse = (const float*)lse_f32; p.delta = (const float*)delta_f32; p.dq = (float*)dq_f32;
     p.dk = (bf16*)dk; p.dv = (bf16*)dv; p.ld_dkv = ld_dkv;
+    { const char* d = getenv("VLB_BW_DBG"); p.dbg = d ? atoi(d) : 0; }
     static bool attr = false;
     if (!attr) {
         e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwCfg::SMEM_BYTES);
         VLB_REQUIRE(e == cudaSuccess, "attn_bwd smem attr: %s", cudaGetErrorString(e));
         attr = true;
     }
-    dim3 grid(S / BW_BK, Hkv, B);
+    p.nkb = S / BW_BK; p.nbh = Hkv * B;
+    dim3 grid((unsigned)(p.nkb * p.nbh));
     attn_bwd_kernel<<<grid, BW_THREADS, BwCfg::SMEM_BYTES, st>>>(p, tq, tk, tv, tdo);
     return check_launch("attn_bwd_kernel");
 }
