@@ -97,16 +97,32 @@ int vlb_hrf_pool_fwd(const void* x, const void* norm_w, const void* ln1_w, const
 int vlb_hrf_pool_finalize(const void* partial_f32, const void* ln2_w, const void* ln2_b, void* pooled,
                           void* hrf, void* keep_scale_f32, int B, int H, int nch, float eps, float drop_p,
                           unsigned long long seed, void* stream);
-int vlb_head_loss(const void* pred, const void* y_f32, void* dpred, void* acc_f32, long long n, void* stream);
+/* n = elements of this rank's [B, P_local] slice; n_total = B * P over all voxel shards (gradient scale 2/n_total). */
+int vlb_head_loss(const void* pred, const void* y_f32, void* dpred, void* acc_f32, long long n, long long n_total,
+                  void* stream);
 int vlb_l2_prefill(const void* W, void* grad_f32, void* acc_f32, long long n, float lambda, int write_grad,
                    void* stream);
 int vlb_loss_finalize(const void* acc_f32, void* out_f32, long long n, float lambda, void* stream);
 int vlb_colsum(const void* d, void* out_f32, int B, long long P, void* stream);
 int vlb_ln2_bwd(const void* dy_f32, const void* keep_scale_f32, const void* pooled, const void* ln2_w,
                 void* dpooled_f32, void* dg2_f32, void* db2_f32, int B, int H, float eps, void* stream);
+/* dx may be NULL (frozen backbone, reference freeze_backbone=True, litmodule.py:86-90): only dg1/db1 are produced. */
 int vlb_hrf_pool_bwd(const void* x, const void* norm_w, const void* ln1_w, const void* wmask_f32,
                      const void* dpooled_f32, void* dx, void* dg1_f32, void* db1_f32, int B, int S, int H,
                      int nch, float eps_rms, float eps_ln, void* stream);
+
+/* ------------------------------------------------------------------ cached pooled features (frozen-backbone baseline)
+ * reference: src/preprocessing/videollama2_vlb_extractfeatures.py + VLB_vllama2_friends_baseline.yaml:26-27 recompute
+ * the frozen backbone every epoch; here (u, sw) = (sum_s w_s LN1hat(x_s), sum_s w_s) is extracted once per sample
+ * (vlb_hrf_pool_fwd with unit LN1 affine -> vlb_pool_reduce) and the head trains from it:
+ * pooled = g1*u + b1*sw (vlb_ln1_affine_fwd) -> vlb_hrf_pool_finalize(nch=1) -> readout; vlb_ln1_affine_bwd adds the
+ * LN1 affine gradients. */
+int vlb_pool_reduce(const void* partial_f32, const void* wmask_f32, void* u_f32, void* sw_f32, int B, int S, int H,
+                    int nch, void* stream);
+int vlb_ln1_affine_fwd(const void* u_f32, const void* sw_f32, const void* ln1_w, const void* ln1_b, void* out_f32,
+                       int B, int H, void* stream);
+int vlb_ln1_affine_bwd(const void* dpooled_f32, const void* u_f32, const void* sw_f32, void* dg1_f32, void* db1_f32,
+                       int B, int H, void* stream);
 
 /* ------------------------------------------------------------------ optimiser (one flat buffer of trainables)
  * clip_grad_norm_(gradient_clip_val=1) + AdamW (decoupled weight decay on every trainable) with the cosine LR value

@@ -160,10 +160,10 @@ __global__ void __launch_bounds__(HT) hrf_pool_finalize_kernel(const float* __re
 
 // d = pred - bf16(y); acc[0] += sum d^2; dpred = bf16(2 d / n)   (F.mse_loss, reduction mean over B*P)
 __global__ void head_loss_kernel(const bf16* __restrict__ pred, const float* __restrict__ y, bf16* __restrict__ dpred,
-                                 float* __restrict__ acc, long long n) {
+                                 float* __restrict__ acc, long long n, long long n_total) {
     __shared__ float red[32];
     float s = 0.f;
-    const float k = 2.f / (float)n;
+    const float k = 2.f / (float)n_total;     // n_total = B * P over ALL voxel shards (== n when the head is not sharded)
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const float d = bf2f(pred[i]) - bf2f(f2bf(y[i]));
         s += d * d;
@@ -294,10 +294,12 @@ __global__ void __launch_bounds__(HT) hrf_pool_bwd_kernel(const bf16* __restrict
         const float wgt = wmask[(size_t)b * S + s];
         bf16* dxr = dx + ((size_t)b * S + s) * H;
         if (wgt == 0.f) {
+            if (dx != nullptr) {
 #pragma unroll
-            for (int i = 0; i < HV; ++i) {
-                const int c = threadIdx.x + i * HT;
-                if (c < nchunk) *reinterpret_cast<uint4*>(dxr + c * 8) = make_uint4(0, 0, 0, 0);
+                for (int i = 0; i < HV; ++i) {
+                    const int c = threadIdx.x + i * HT;
+                    if (c < nchunk) *reinterpret_cast<uint4*>(dxr + c * 8) = make_uint4(0, 0, 0, 0);
+                }
             }
             continue;
         }
@@ -324,6 +326,7 @@ __global__ void __launch_bounds__(HT) hrf_pool_bwd_kernel(const bf16* __restrict
                 }
             }
         }
+        if (dx == nullptr) continue;          // frozen backbone: only the LN1 gradients are needed
         m1 = block_sum(m1, red) / (float)H;
         m2 = block_sum(m2, red) / (float)H;
         // RMSNorm backward: y = wn * (x * rstd); g = gz * wn; dx = rstd * (g - xh * mean(g * xh))
@@ -368,6 +371,55 @@ __global__ void __launch_bounds__(HT) hrf_pool_bwd_kernel(const bf16* __restrict
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------- cached features
+// With a frozen backbone the LN1 affine commutes with the pooling: sum_s w_s (g1 * n_s + b1) = g1 * u + b1 * sw with
+// u = sum_s w_s n_s and sw = sum_s w_s, so (u, sw) is a per-sample feature that never changes while the head trains.
+// pool_reduce: partial[b, nch, H] (hrf_pool_fwd run with g1 = 1, b1 = 0) -> u[b, H] fp32 ; sw[b] = sum_s wmask[b, s]
+__global__ void __launch_bounds__(HT) pool_reduce_kernel(const float* __restrict__ partial, const float* __restrict__ wmask,
+                                                         float* __restrict__ u, float* __restrict__ sw, int nch, int H, int S) {
+    __shared__ float red[32];
+    const int b = blockIdx.x, nchunk = H / 8;
+    for (int c = threadIdx.x; c < nchunk; c += HT) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = 0.f;
+        for (int k = 0; k < nch; ++k) {
+            float t[8]; load8(partial + ((size_t)b * nch + k) * H + c * 8, t);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += t[j];
+        }
+        store8(u + (size_t)b * H + c * 8, v);
+    }
+    float s = 0.f;
+    for (int i = threadIdx.x; i < S; i += HT) s += wmask[(size_t)b * S + i];
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) sw[b] = s;
+}
+
+// pooled_pre[b, h] = g1[h] * u[b, h] + b1[h] * sw[b]   (fp32; consumed by hrf_pool_finalize with nch = 1)
+__global__ void ln1_affine_fwd_kernel(const float* __restrict__ u, const float* __restrict__ sw, const bf16* __restrict__ g1,
+                                      const bf16* __restrict__ b1, float* __restrict__ out, int B, int H) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= (long long)B * H) return;
+    const int h = (int)(i % H); const int b = (int)(i / H);
+    out[i] = bf2f(g1[h]) * u[i] + bf2f(b1[h]) * sw[b];
+}
+
+// dg1[h] += sum_b dpooled[b, h] * u[b, h] ; db1[h] += sum_b dpooled[b, h] * sw[b]
+__global__ void ln1_affine_bwd_kernel(const float* __restrict__ dpooled, const float* __restrict__ u,
+                                      const float* __restrict__ sw, float* __restrict__ dg1, float* __restrict__ db1,
+                                      int B, int H) {
+    const int h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= H) return;
+    float ag = 0.f, ab = 0.f;
+    for (int b = 0; b < B; ++b) {
+        const float d = dpooled[(size_t)b * H + h];
+        ag += d * u[(size_t)b * H + h]; ab += d * sw[b];
+    }
+    dg1[h] += ag; db1[h] += ab;
+}
+
 }  // namespace vlb
 
 using namespace vlb;
@@ -394,10 +446,11 @@ extern "C" int vlb_hrf_pool_finalize(const void* partial_f32, const void* ln2_w,
 }
 
 extern "C" int vlb_head_loss(const void* pred, const void* y_f32, void* dpred, void* acc_f32, long long n,
-                             void* stream) {
+                             long long n_total, void* stream) {
+    VLB_REQUIRE(n_total >= n && n > 0, "head_loss: n=%lld n_total=%lld", n, n_total);
     int grid = (int)((n + 255) / 256); if (grid > num_sms() * 8) grid = num_sms() * 8;
     head_loss_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)pred, (const float*)y_f32, (bf16*)dpred,
-                                                            (float*)acc_f32, n);
+                                                            (float*)acc_f32, n, n_total);
     return check_launch("head_loss");
 }
 
@@ -439,4 +492,27 @@ extern "C" int vlb_hrf_pool_bwd(const void* x, const void* norm_w, const void* l
         (const bf16*)x, (const bf16*)norm_w, (const bf16*)ln1_w, (const float*)wmask_f32, (const float*)dpooled_f32,
         (bf16*)dx, (float*)dg1_f32, (float*)db1_f32, S, H, rows_per, eps_rms, eps_ln);
     return check_launch("hrf_pool_bwd");
+}
+
+extern "C" int vlb_pool_reduce(const void* partial_f32, const void* wmask_f32, void* u_f32, void* sw_f32, int B, int S,
+                               int H, int nch, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && B > 0 && nch > 0, "pool_reduce: B=%d H=%d nch=%d", B, H, nch);
+    pool_reduce_kernel<<<B, HT, 0, (cudaStream_t)stream>>>((const float*)partial_f32, (const float*)wmask_f32, (float*)u_f32,
+                                                          (float*)sw_f32, nch, H, S);
+    return check_launch("pool_reduce");
+}
+
+extern "C" int vlb_ln1_affine_fwd(const void* u_f32, const void* sw_f32, const void* ln1_w, const void* ln1_b,
+                                  void* out_f32, int B, int H, void* stream) {
+    const long long n = (long long)B * H;
+    ln1_affine_fwd_kernel<<<(unsigned)ceil_div_ll(n, 256), 256, 0, (cudaStream_t)stream>>>(
+        (const float*)u_f32, (const float*)sw_f32, (const bf16*)ln1_w, (const bf16*)ln1_b, (float*)out_f32, B, H);
+    return check_launch("ln1_affine_fwd");
+}
+
+extern "C" int vlb_ln1_affine_bwd(const void* dpooled_f32, const void* u_f32, const void* sw_f32, void* dg1_f32,
+                                  void* db1_f32, int B, int H, void* stream) {
+    ln1_affine_bwd_kernel<<<ceil_div(H, 128), 128, 0, (cudaStream_t)stream>>>(
+        (const float*)dpooled_f32, (const float*)u_f32, (const float*)sw_f32, (float*)dg1_f32, (float*)db1_f32, B, H);
+    return check_launch("ln1_affine_bwd");
 }

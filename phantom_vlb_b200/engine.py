@@ -28,6 +28,7 @@ class Engine:
         if lora_dropout:
             raise NotImplementedError("lora_dropout > 0 is not implemented (parity and benchmark runs use 0)")
         self.saved = None
+        self.shard_reduce = None    # callable(tensor): in-place sum across voxel shards of the readout head (config 4)
         self.launches = 0
         self.profile = None
         self._bufs = {}
@@ -145,25 +146,39 @@ class Engine:
         """x0 [B*S, H] (buffer L0_x) -> pre-final-norm hidden [B*S, H]."""
         cfg, W, T = self.cfg, self.W, self.T
         S, M, D, s = cfg.max_len, B * cfg.max_len, cfg.head_dim, self.scale
+        lora = cfg.use_lora
+        assert lora or not save, "a frozen backbone (use_lora=False) has no decoder backward: call with save=False"
         x = x0
         for l, L in enumerate(W.llm_layers):
             b = self._layer_bufs(l if save else 0, M)
             p = "layers.%d." % l
-            bc = T.bcat[l]
+            bc = T.bcat[l] if lora else None
             nxt = self.buf("L%d_x" % (l + 1), (M, cfg.hidden)) if save else self.buf("Lx_%d" % (l & 1), (M, cfg.hidden))
             ops.rmsnorm_fwd(x, L["ln1_w"], cfg.rms_eps, out=b["xn1"], rstd=b["rstd1"])
-            self.gemm(b["xn1"], T.w(p + "Acat_qkv"), b["xa1"], alpha=s)
-            self.gemm(b["xn1"], L["wqkv"], b["qkv"], a2=b["xa1"], b2=bc["qkv"])
+            if lora:
+                self.gemm(b["xn1"], T.w(p + "Acat_qkv"), b["xa1"], alpha=s)
+                self.gemm(b["xn1"], L["wqkv"], b["qkv"], a2=b["xa1"], b2=bc["qkv"])
+            else:
+                self.gemm(b["xn1"], L["wqkv"], b["qkv"])
             ops.rope_(b["qkv"], W.llm["cos"], W.llm["sin"], S, cfg.heads + cfg.kv_heads, D)
             ops.attn_fwd_into(b["qkv"], b["o"], b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True)
-            self.gemm(b["o"], T.w(p + "A_o"), b["xa2"], alpha=s)
-            self.gemm(b["o"], L["wo"], b["h1"], a2=b["xa2"], b2=bc["o"], residual=x)
+            if lora:
+                self.gemm(b["o"], T.w(p + "A_o"), b["xa2"], alpha=s)
+                self.gemm(b["o"], L["wo"], b["h1"], a2=b["xa2"], b2=bc["o"], residual=x)
+            else:
+                self.gemm(b["o"], L["wo"], b["h1"], residual=x)
             ops.rmsnorm_fwd(b["h1"], L["ln2_w"], cfg.rms_eps, out=b["xn2"], rstd=b["rstd2"])
-            self.gemm(b["xn2"], T.w(p + "Acat_gu"), b["xa3"], alpha=s)
-            self.gemm(b["xn2"], L["wgu"], b["gu"], a2=b["xa3"], b2=bc["gu"])
+            if lora:
+                self.gemm(b["xn2"], T.w(p + "Acat_gu"), b["xa3"], alpha=s)
+                self.gemm(b["xn2"], L["wgu"], b["gu"], a2=b["xa3"], b2=bc["gu"])
+            else:
+                self.gemm(b["xn2"], L["wgu"], b["gu"])
             ops.swiglu_fwd(b["gu"], out=b["act"])
-            self.gemm(b["act"], T.w(p + "A_d"), b["xa4"], alpha=s)
-            self.gemm(b["act"], L["wd"], nxt, a2=b["xa4"], b2=bc["d"], residual=b["h1"])
+            if lora:
+                self.gemm(b["act"], T.w(p + "A_d"), b["xa4"], alpha=s)
+                self.gemm(b["act"], L["wd"], nxt, a2=b["xa4"], b2=bc["d"], residual=b["h1"])
+            else:
+                self.gemm(b["act"], L["wd"], nxt, residual=b["h1"])
             self.launches += 5
             x = nxt
         return x
@@ -251,16 +266,35 @@ class Engine:
         return hidden, wm
 
     # ------------------------------------------------------------------ brain head
-    def head_forward(self, hidden, wm, y, B, training):
+    def _nch(self):
+        S = self.cfg.max_len
+        return 64 if S >= 1024 else max(1, S // 16)
+
+    def _pool_partial(self, hidden, wm, B, unit_affine=False):
+        """final RMSNorm + LN1 + HRF pooling of [B*S, H] -> fp32 partial sums [B, nch, H] (one read of `hidden`)."""
         cfg, T = self.cfg, self.T
-        H, P, S = cfg.hidden, cfg.num_target, cfg.max_len
-        nch = 64 if S >= 1024 else max(1, S // 16)
+        H, S, nch = cfg.hidden, cfg.max_len, self._nch()
         partial = self.buf("hd_partial", (B, nch, H), torch.float32)
+        if unit_affine:         # feature extraction: LN1 affine factored out of the pooling (see vlb_pool_reduce)
+            g1 = self.buf("hd_ones", (H,)); b1 = self.buf("hd_zeros", (H,))
+            g1.fill_(1.0); b1.zero_()
+        else:
+            g1, b1 = T.w("ln1_w"), T.w("ln1_b")
+        _l.call("vlb_hrf_pool_fwd", _l.ptr(hidden), _l.ptr(self.W.llm["norm_w"]), _l.ptr(g1), _l.ptr(b1),
+                _l.ptr(wm), _l.ptr(partial), B, S, H, nch, cfg.rms_eps, cfg.head_ln_eps, _l.cur_stream())
+        self.launches += 1
+        return partial, nch
+
+    def head_forward(self, hidden, wm, y, B, training, partial=None, nch=None):
+        """LN2 -> dropout -> readout -> MSE + ridge penalty. `y` is this rank's [B, P_local] target slice; with a
+        voxel-sharded head (`self.shard_reduce` set) the loss partial sums are summed across ranks before finalize."""
+        cfg, T = self.cfg, self.T
+        H, P = cfg.hidden, T.num_target_local
+        if partial is None:
+            partial, nch = self._pool_partial(hidden, wm, B)
         pooled, hrf = self.buf("hd_pooled", (B, H)), self.buf("hd_hrf", (B, H))
         drop = self.dropout_rate if training else 0.0
         keep = self.buf("hd_keep", (B, H), torch.float32) if drop > 0 else None
-        _l.call("vlb_hrf_pool_fwd", _l.ptr(hidden), _l.ptr(self.W.llm["norm_w"]), _l.ptr(T.w("ln1_w")), _l.ptr(T.w("ln1_b")),
-                _l.ptr(wm), _l.ptr(partial), B, S, H, nch, cfg.rms_eps, cfg.head_ln_eps, _l.cur_stream())
         self.rng_step = getattr(self, "rng_step", 0) + 1
         _l.call("vlb_hrf_pool_finalize", _l.ptr(partial), _l.ptr(T.w("ln2_w")), _l.ptr(T.w("ln2_b")), _l.ptr(pooled),
                 _l.ptr(hrf), _l.ptr(keep), B, H, nch, cfg.head_ln_eps, float(drop), 0x5EED0000 + self.rng_step, _l.cur_stream())
@@ -269,41 +303,60 @@ class Engine:
         acc.zero_()
         dpred = self.buf("hd_dpred", (B, P))
         out = self.buf("hd_loss", (3,), torch.float32)
-        _l.call("vlb_head_loss", _l.ptr(pred), _l.ptr(y), _l.ptr(dpred), _l.ptr(acc), B * P, _l.cur_stream())
+        n_total = B * cfg.num_target
+        assert y.shape == (B, P) and y.dtype == torch.float32
+        _l.call("vlb_head_loss", _l.ptr(pred), _l.ptr(y), _l.ptr(dpred), _l.ptr(acc), B * P, n_total, _l.cur_stream())
         _l.call("vlb_l2_prefill", _l.ptr(T.w("ridge_w")), _l.ptr(T.g("ridge_w")), _l.ptr(acc), P * H, cfg.l2_lambda,
                 int(training), _l.cur_stream())
-        _l.call("vlb_loss_finalize", _l.ptr(acc), _l.ptr(out), B * P, cfg.l2_lambda, _l.cur_stream())
-        self.launches += 5
+        if self.shard_reduce is not None:
+            self.shard_reduce(acc)
+        _l.call("vlb_loss_finalize", _l.ptr(acc), _l.ptr(out), n_total, cfg.l2_lambda, _l.cur_stream())
+        self.launches += 4
         self.head_saved = dict(pooled=pooled, hrf=hrf, keep=keep, dpred=dpred, pred=pred, nch=nch)
         return out, pred
 
-    def head_backward(self, hidden, wm, B):
-        """Gradients of ridge W/b, LN1/LN2 into T.grad; returns d(loss)/d(pre-final-norm hidden) [B*S, H] bf16."""
+    def _head_backward_to_pooled(self, B):
+        """ridge W/b and LN2 gradients into T.grad; returns d(loss)/d(pooled) fp32 [B, H]."""
         cfg, T, hs = self.cfg, self.T, self.head_saved
-        H, P, S = cfg.hidden, cfg.num_target, cfg.max_len
+        H, P = cfg.hidden, T.num_target_local
         self.gemm(hs["dpred"], hs["hrf"], T.g("ridge_w"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
         _l.call("vlb_colsum", _l.ptr(hs["dpred"]), _l.ptr(T.g("ridge_b")), B, P, _l.cur_stream())
         dhrf = self.gemm(hs["dpred"], T.w("ridge_w"), self.buf("hd_dhrf", (B, H), torch.float32), b_mn=True, out_f32=True)
+        if self.shard_reduce is not None:
+            self.shard_reduce(dhrf)         # each voxel shard contributes a partial d(hrf); LN grads end up replicated
         dpooled = self.buf("hd_dpooled", (B, H), torch.float32)
         _l.call("vlb_ln2_bwd", _l.ptr(dhrf), _l.ptr(hs["keep"]), _l.ptr(hs["pooled"]), _l.ptr(T.w("ln2_w")), _l.ptr(dpooled),
                 _l.ptr(T.g("ln2_w")), _l.ptr(T.g("ln2_b")), B, H, cfg.head_ln_eps, _l.cur_stream())
-        dx = self.buf("bw_dx_a", (B * S, H))
+        self.launches += 2
+        return dpooled
+
+    def head_backward(self, hidden, wm, B, need_dx=True):
+        """Gradients of ridge W/b, LN1/LN2 into T.grad; returns d(loss)/d(pre-final-norm hidden) [B*S, H] bf16
+        (None when need_dx is False: frozen backbone, only the LN1 gradients are accumulated)."""
+        cfg, T, hs = self.cfg, self.T, self.head_saved
+        H, S = cfg.hidden, cfg.max_len
+        dpooled = self._head_backward_to_pooled(B)
+        dx = self.buf("bw_dx_a", (B * S, H)) if need_dx else None
         _l.call("vlb_hrf_pool_bwd", _l.ptr(hidden), _l.ptr(self.W.llm["norm_w"]), _l.ptr(T.w("ln1_w")), _l.ptr(wm),
                 _l.ptr(dpooled), _l.ptr(dx), _l.ptr(T.g("ln1_w")), _l.ptr(T.g("ln1_b")), B, S, H, hs["nch"], cfg.rms_eps,
                 cfg.head_ln_eps, _l.cur_stream())
-        self.launches += 3
+        self.launches += 1
         return dx
 
     # ------------------------------------------------------------------ steps
     def loss_and_grads(self, batch):
-        """One forward + backward of training_step (litmodule.py:259-306). Returns (loss[3] fp32 device tensor, pred)."""
+        """One forward + backward of training_step (litmodule.py:259-306). Returns (loss[3] fp32 device tensor, pred).
+        LoRA mode back-propagates through the decoder; the frozen-backbone baseline (use_lora=False, reference
+        freeze_backbone=True litmodule.py:86-90) keeps no activations and stops at the head."""
         B = batch["vision"].shape[0]
+        lora = self.cfg.use_lora
         self.T.grad.zero_()      # every gradient kernel below ACCUMULATES (split-K red.add GEMMs, LN atomics)
-        hidden, wm = self.backbone_forward(batch, save=True)
+        hidden, wm = self.backbone_forward(batch, save=lora)
         y = batch["timeseries"].contiguous()
         out, pred = self.head_forward(hidden, wm, y, B, training=True)
-        dx = self.head_backward(hidden, wm, B)
-        self.decoder_backward(dx, B)
+        dx = self.head_backward(hidden, wm, B, need_dx=lora)
+        if lora:
+            self.decoder_backward(dx, B)
         return out, pred
 
     def eval_step(self, batch):
@@ -312,6 +365,40 @@ class Engine:
         hidden, wm = self.backbone_forward(batch, save=False)
         return self.head_forward(hidden, wm, batch["timeseries"].contiguous(), B, training=False)
 
+    # ------------------------------------------------------------------ frozen-backbone feature cache
+    def extract_features(self, batch, out_u=None, out_sw=None):
+        """Backbone forward only -> (u fp32 [B, H], sw fp32 [B]) with u = sum_s w_s LN1hat(RMSNorm(h_s)), sw = sum_s w_s.
+        While the backbone is frozen these never change, so the head can train from them without re-running the
+        34-39 TF/clip forward every epoch (the reference recomputes it: VLB_vllama2_friends_baseline.yaml:26-27)."""
+        cfg = self.cfg
+        B, H, S = batch["vision"].shape[0], cfg.hidden, cfg.max_len
+        hidden, wm = self.backbone_forward(batch, save=False)
+        partial, nch = self._pool_partial(hidden, wm, B, unit_affine=True)
+        u = out_u if out_u is not None else torch.empty((B, H), device=self.dev, dtype=torch.float32)
+        sw = out_sw if out_sw is not None else torch.empty((B,), device=self.dev, dtype=torch.float32)
+        _l.call("vlb_pool_reduce", _l.ptr(partial), _l.ptr(wm), _l.ptr(u), _l.ptr(sw), B, S, H, nch, _l.cur_stream())
+        self.launches += 1
+        return u, sw
+
+    def cached_loss_and_grads(self, u, sw, y, training=True):
+        """Head-only train step from cached features: pooled = g1*u + b1*sw -> LN2 -> dropout -> readout -> loss, and the
+        ridge / LN1 / LN2 gradients. u [B, H] fp32, sw [B] fp32, y [B, P_local] fp32 (all B samples, this rank's voxels)."""
+        cfg, T = self.cfg, self.T
+        B, H = u.shape
+        if training:
+            T.grad.zero_()
+        pre = self.buf("hd_partial1", (B, 1, H), torch.float32)
+        _l.call("vlb_ln1_affine_fwd", _l.ptr(u), _l.ptr(sw), _l.ptr(T.w("ln1_w")), _l.ptr(T.w("ln1_b")), _l.ptr(pre), B, H,
+                _l.cur_stream())
+        out, pred = self.head_forward(None, None, y.contiguous(), B, training=training, partial=pre, nch=1)
+        self.launches += 1
+        if training:
+            dpooled = self._head_backward_to_pooled(B)
+            _l.call("vlb_ln1_affine_bwd", _l.ptr(dpooled), _l.ptr(u), _l.ptr(sw), _l.ptr(T.g("ln1_w")), _l.ptr(T.g("ln1_b")),
+                    B, H, _l.cur_stream())
+            self.launches += 1
+        return out, pred
+
     def optimizer_step(self, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, max_norm=1.0, world_size=1,
                        allreduce=None):
         """clip_grad_norm_(max_norm) + AdamW on the flat buffer; `allreduce(tensor)` sums gradients across ranks first."""
@@ -319,13 +406,22 @@ class Engine:
         if allreduce is not None:
             allreduce(T.grad)
         T.sumsq.zero_()
-        _l.call("vlb_grad_sumsq", _l.ptr(T.grad), T.numel, _l.ptr(T.sumsq), _l.cur_stream())
+        if self.shard_reduce is None:
+            _l.call("vlb_grad_sumsq", _l.ptr(T.grad), T.numel, _l.ptr(T.sumsq), _l.cur_stream())
+        else:
+            # voxel-sharded head: ridge W/b gradients are rank-private (sum their squares across ranks), the LN1/LN2
+            # gradients that follow them in the flat buffer are replicated (count them once)
+            split = T.offsets["ln1_w"][0]
+            _l.call("vlb_grad_sumsq", _l.ptr(T.grad), split, _l.ptr(T.sumsq), _l.cur_stream())
+            self.shard_reduce(T.sumsq)
+            _l.call("vlb_grad_sumsq", T.grad.data_ptr() + 4 * split, T.numel - split, _l.ptr(T.sumsq), _l.cur_stream())
+            self.launches += 1
         T.step_count += 1
         _l.call("vlb_adamw_step", _l.ptr(T.param), _l.ptr(T.grad), _l.ptr(T.m), _l.ptr(T.v), _l.ptr(T.param_bf16), T.numel,
                 _l.ptr(T.sumsq), float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), T.step_count,
                 float(max_norm), 1.0 / world_size, _l.cur_stream())
         T.stage_b()
-        self.launches += 2 + 7 * self.cfg.layers
+        self.launches += 2 + 7 * T.lora_layers
 
     def train_step(self, batch, lr, **opt):
         out, _ = self.loss_and_grads(batch)

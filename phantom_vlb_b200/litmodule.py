@@ -65,7 +65,7 @@ class VLBLitModuleConfig:
 def model_config_for(config: VLBLitModuleConfig, num_frames=8) -> ModelConfig:
     kind = str(config.model_path).split(":")[-1].lower()
     common = dict(num_target=config.num_target, l2_lambda=config.l2_lambda, num_frames=num_frames,
-                  lora_r=config.lora_r or 16, lora_alpha=config.lora_alpha or 32)
+                  lora_r=config.lora_r or 16, lora_alpha=config.lora_alpha or 32, use_lora=bool(config.use_lora))
     if kind in ("7b", "videollama2-7b"):
         return ModelConfig(**common)
     if kind == "config1":
@@ -122,23 +122,26 @@ class VLBLitModule(LightningModule):
         self.engine = None
 
     # ------------------------------------------------------------------ model construction (litmodule.py:206-226)
-    def configure_model(self, frozen=None, model_config: ModelConfig = None, device="cuda", seed=1234, lora_b_std=0.0):
+    def configure_model(self, frozen=None, model_config: ModelConfig = None, device="cuda", seed=1234, lora_b_std=0.0,
+                        target_slice=None):
         if self.engine is not None:
             return
-        if not self.config.use_lora or self.config.freeze_backbone:
-            raise NotImplementedError("only the LoRA experiment (use_lora=True, freeze_backbone=False) is built; the "
-                                      "frozen-backbone baseline is SURVEY 8(f-2)")
+        # the two experiments the reference ships (config/experiment/*.yaml): LoRA (use_lora, backbone otherwise frozen)
+        # and the frozen-backbone baseline (freeze_backbone=True, use_lora=False: head-only training)
+        if self.config.use_lora == self.config.freeze_backbone:
+            raise NotImplementedError("full fine-tuning (use_lora=False, freeze_backbone=False) is not built, and "
+                                      "use_lora=True with freeze_backbone=True is contradictory (litmodule.py:86-120)")
         mc = model_config or model_config_for(self.config)
         dev = torch.device(device)
         W = frozen if frozen is not None else frozen_random(mc, dev, seed)
-        T = Trainables(mc, dev)
+        T = Trainables(mc, dev, target_slice=target_slice)
         T.init_default(seed, lora_b_std=lora_b_std)
         self.engine = Engine(mc, W, T, device=dev, dropout_rate=self.config.dropout_rate,
                              lora_dropout=self.config.lora_dropout or 0.0)
         self.model_config = mc
         self.flat = torch.nn.Parameter(T.param)           # aliases the fp32 master buffer
         self.hrf_layer = HRFConvolveLayer()
-        self.ridge_layer = RidgeRegressionLayer(mc.hidden, self.config.num_target, self.config.l2_lambda)
+        self.ridge_layer = RidgeRegressionLayer(mc.hidden, T.num_target_local, self.config.l2_lambda)
         self._params_dirty = False
 
     def named_trainables(self):

@@ -48,6 +48,7 @@ class ModelConfig:
     l2_lambda: float = 0.001
     head_ln_eps: float = 1e-5
     lang_w_len: int = 64
+    use_lora: bool = True          # False: frozen-backbone baseline (VLB_vllama2_friends_baseline.yaml:26-27), head-only training
 
     @property
     def grid(self):
@@ -246,18 +247,22 @@ class Trainables:
     """One flat fp32 master buffer (+ grad, Adam m/v, bf16 working copy) holding every trainable tensor, so that the
     data-parallel all-reduce, the global-norm clip and AdamW are each ONE pass over one contiguous buffer."""
 
-    def __init__(self, cfg, dev):
+    def __init__(self, cfg, dev, target_slice=None):
+        """target_slice=(lo, hi): this rank owns readout rows [lo, hi) of the P voxels (head sharded by voxel, SURVEY 8e
+        config 4); None = all of them."""
         self.cfg, self.dev = cfg, dev
         r, H, I, D = cfg.lora_r, cfg.hidden, cfg.mlp, cfg.head_dim
         nq, nkv = cfg.heads * D, cfg.kv_heads * D
+        self.target_slice = (0, cfg.num_target) if target_slice is None else (int(target_slice[0]), int(target_slice[1]))
+        self.lora_layers = cfg.layers if cfg.use_lora else 0
         self.spec = []
-        for l in range(cfg.layers):
+        for l in range(self.lora_layers):
             p = "layers.%d." % l
             self.spec += [(p + "Acat_qkv", (3 * r, H)), (p + "Bt_q", (r, nq)), (p + "Bt_k", (r, nkv)), (p + "Bt_v", (r, nkv)),
                           (p + "A_o", (r, nq)), (p + "Bt_o", (r, H)),
                           (p + "Acat_gu", (2 * r, H)), (p + "Bt_g", (r, I)), (p + "Bt_u", (r, I)),
                           (p + "A_d", (r, I)), (p + "Bt_d", (r, H))]
-        P = cfg.num_target
+        P = self.num_target_local = self.target_slice[1] - self.target_slice[0]
         self.spec += [("ridge_w", (P, H)), ("ridge_b", (P,)), ("ln1_w", (H,)), ("ln1_b", (H,)), ("ln2_w", (H,)), ("ln2_b", (H,))]
         self.offsets, off = {}, 0
         for name, shape in self.spec:
@@ -272,7 +277,7 @@ class Trainables:
         self.step_count = 0
         # bf16 block-diagonal / transposed staging of the LoRA B matrices for the forward fused k-block
         self.bcat = []
-        for l in range(cfg.layers):
+        for l in range(self.lora_layers):
             self.bcat.append(dict(qkv=torch.zeros((nq + 2 * nkv, 3 * r), device=dev, dtype=torch.bfloat16),
                                   o=torch.zeros((H, r), device=dev, dtype=torch.bfloat16),
                                   gu=torch.zeros((2 * I, 2 * r), device=dev, dtype=torch.bfloat16),
@@ -313,6 +318,8 @@ class Trainables:
     def load_from_oracle(self, ref):
         """Copy LoRA + head parameters of an oracle RefVLB into the flat master (test-side helper)."""
         for l, layer in enumerate(ref.llm.layers):
+            if l >= self.lora_layers:
+                break
             a, m = layer.self_attn, layer.mlp
             p = "layers.%d." % l
             self.p(p + "Acat_qkv").copy_(torch.cat([a.q_proj.lora_A.weight, a.k_proj.lora_A.weight, a.v_proj.lora_A.weight], 0))
@@ -326,8 +333,9 @@ class Trainables:
             self.p(p + "Bt_u").copy_(m.up_proj.lora_B.weight.t())
             self.p(p + "A_d").copy_(m.down_proj.lora_A.weight)
             self.p(p + "Bt_d").copy_(m.down_proj.lora_B.weight.t())
-        self.p("ridge_w").copy_(ref.ridge.weight)
-        self.p("ridge_b").copy_(ref.ridge.bias)
+        lo, hi = self.target_slice
+        self.p("ridge_w").copy_(ref.ridge.weight[lo:hi])
+        self.p("ridge_b").copy_(ref.ridge.bias[lo:hi])
         self.p("ln1_w").copy_(ref.layer_norm1.weight); self.p("ln1_b").copy_(ref.layer_norm1.bias)
         self.p("ln2_w").copy_(ref.layer_norm2.weight); self.p("ln2_b").copy_(ref.layer_norm2.bias)
         self.sync_working()
@@ -342,7 +350,7 @@ class Trainables:
         cfg = self.cfg
         r, D = cfg.lora_r, cfg.head_dim
         nq, nkv, I = cfg.heads * D, cfg.kv_heads * D, cfg.mlp
-        for l in range(cfg.layers):
+        for l in range(self.lora_layers):
             p = "layers.%d." % l
             bc = self.bcat[l]
             ops.copy2d(self.w(p + "Bt_q"), bc["qkv"][0:nq, 0:r], r, nq, transpose=True)
