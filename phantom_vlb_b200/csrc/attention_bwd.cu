@@ -59,6 +59,7 @@ struct BwParams {
     bf16* dk; bf16* dv;     // rows [B*S], row stride ld_dkv, head hk at column hk*D
     int ld_dkv;
     int nkb, nbh;           // key blocks per sequence, Hkv * B
+    int chunk;              // batch elements per dispatch chunk
     int dbg;                // VLB_BW_DBG timing experiments (bit0: skip dQ reduction, bit1: skip exp2) -- never set in product runs
 };
 
@@ -87,9 +88,16 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // heaviest key blocks (j = 0 sees every query block) are dispatched first
-    const int j = blockIdx.x / p.nbh;
-    const int hk = (blockIdx.x % p.nbh) % p.Hkv, b = (blockIdx.x % p.nbh) / p.Hkv;
+    // (batch, kv head)-major dispatch keeps the fp32 dQ rows that co-resident CTAs reduce into (4 heads x S x 128 x 4 B
+    // = 4 MB per group) inside L2; a key-block-major order touched the whole 268 MB dQ buffer per wave and turned the
+    // red.adds into DRAM read-modify-writes (ncu r01b: 3.4 GB of DRAM traffic per launch at B=8). Within a group the
+    // heaviest key blocks (j = 0 sees every query block) go first.
+    // order: batch chunks of p.chunk elements; inside a chunk key-block-major (heaviest first), then kv head, batch
+    const int per_chunk = p.nkb * p.Hkv * p.chunk;
+    const int c_ = blockIdx.x / per_chunk, r_ = blockIdx.x % per_chunk;
+    const int nb_c = min(p.chunk, p.nbh / p.Hkv - c_ * p.chunk);      // batch elements in this chunk (last may be short)
+    const int j = r_ / (p.Hkv * nb_c);
+    const int hk = (r_ % (p.Hkv * nb_c)) % p.Hkv, b = c_ * p.chunk + (r_ % (p.Hkv * nb_c)) / p.Hkv;
     const int k0 = j * BW_BK;
     const int nq = p.S / BW_BQ;
     const int i_start = p.causal ? (k0 / BW_BQ) : 0;
@@ -375,6 +383,9 @@ extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_
         attr = true;
     }
     p.nkb = S / BW_BK; p.nbh = Hkv * B;
+    // two batch elements per dispatch chunk: their fp32 dQ rows (2 x 32 heads x S x 128 x 4 B = 67 MB at S=2048) stay in
+    // the 126 MB L2 while all key blocks reduce into them; measured at B=8: chunk 1/2/4/8 -> 1.078/1.065/1.071/1.118 ms
+    p.chunk = B < 2 ? B : 2;
     dim3 grid((unsigned)(p.nkb * p.nbh));
     attn_bwd_kernel<<<grid, BW_THREADS, BwCfg::SMEM_BYTES, st>>>(p, tq, tk, tv, tdo);
     return check_launch("attn_bwd_kernel");
