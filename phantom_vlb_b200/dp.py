@@ -81,3 +81,27 @@ def shard_columns(P, rank, world_size, align=8):
     lo = min(P, rank * per)
     hi = min(P, lo + per)
     return lo, hi
+
+
+def gather_rows(t, group=None):
+    """All-gather along dim 0 in rank order: [B, ...] on every rank -> [world*B, ...] (the pooled features of config 4:
+    every voxel shard of the readout head sees every clip of the global batch)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return t
+    w = dist.get_world_size(group)
+    out = torch.empty((w * t.shape[0],) + tuple(t.shape[1:]), device=t.device, dtype=t.dtype)
+    dist.all_gather_into_tensor(out, t.contiguous(), group=group)
+    return out
+
+
+def make_sum_reducer(group=None):
+    """callable(tensor) -> in-place sum across ranks, or None for a single process. Installed as Engine.shard_reduce when
+    the readout head is sharded by voxel: it is applied to the loss partial sums [2], to d(hrf) [B, H] and to the squared
+    gradient norm of the rank-private ridge slice."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return None
+
+    def reduce(t):
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        return t
+    return reduce

@@ -1,5 +1,6 @@
 """World-size-2 gloo tests of the data-parallel host logic (phantom_vlb_b200/dp.py): sampler sharding, the gradient
-all-reduce + 1/world folding contract of the optimiser front-end, and the Pearson moment merge.  CPU only; the CUDA
+all-reduce + 1/world folding contract of the optimiser front-end, the Pearson moment merge, and the voxel-sharded
+readout head (feature all-gather, loss / d(hrf) / norm partial sums).  CPU only; the CUDA
 kernels on either side of these collectives are covered by the -m gpu tests."""
 import os
 import socket
@@ -53,6 +54,37 @@ def _worker(rank, world, port, q):
         assert n == 501
         r = pearson_from_stats(st.numpy(), n)
         assert np.allclose(r, pearson_r(x, y), atol=1e-12)
+        # ---- config 4: readout head sharded by voxel. Features are all-gathered in rank order, each rank computes its
+        # voxel slice for ALL clips, and only the loss partial sums, d(hrf) and the ridge-slice squared norm are summed.
+        torch.manual_seed(3)
+        Bl, H, P = 3, 16, 43
+        feats_all = torch.randn(world * Bl, H, dtype=torch.float64)
+        W = torch.randn(P, H, dtype=torch.float64, requires_grad=True)
+        y_all = torch.randn(world * Bl, P, dtype=torch.float64)
+        hrf_full = feats_all.clone().requires_grad_(True)
+        loss_full = ((hrf_full @ W.t() - y_all) ** 2).mean() + 1e-3 * (W ** 2).sum()
+        loss_full.backward()
+        mine = feats_all[rank * Bl:(rank + 1) * Bl].contiguous()
+        gathered = dp.gather_rows(mine)
+        assert torch.equal(gathered, feats_all)
+        reduce = dp.make_sum_reducer()
+        assert reduce is not None
+        lo, hi = dp.shard_columns(P, rank, world)
+        Wl = W.detach()[lo:hi]
+        d = gathered @ Wl.t() - y_all[:, lo:hi]
+        acc = torch.tensor([float((d ** 2).sum()), float((Wl ** 2).sum())], dtype=torch.float64)
+        reduce(acc)
+        n_total = world * Bl * P
+        assert abs(float(acc[0] / n_total + 1e-3 * acc[1]) - float(loss_full)) < 1e-12
+        dpred = 2 * d / n_total
+        dhrf = dpred @ Wl
+        reduce(dhrf)
+        assert torch.allclose(dhrf, hrf_full.grad, atol=1e-12)
+        gW = dpred.t() @ gathered + 2e-3 * Wl
+        assert torch.allclose(gW, W.grad[lo:hi], atol=1e-12)
+        sq = torch.tensor([float((gW ** 2).sum())], dtype=torch.float64)
+        reduce(sq)
+        assert abs(float(sq) - float((W.grad ** 2).sum())) < 1e-9
         q.put((rank, "ok"))
     except Exception as e:                                           # pragma: no cover
         q.put((rank, repr(e)))
