@@ -149,6 +149,60 @@ class VLBLitModule(LightningModule):
         T = self.engine.T
         return [(n, T.p(n)) for n, _ in T.spec]
 
+    # ------------------------------------------------------------------ adapter-only checkpoints
+    # train.py:58-60 saves the full ~16 GB state dict and leaves "saving only LoRA adapters" as a TODO; here the checkpoint
+    # holds the trainable tensors only (LoRA A/B + head, ~184 MB fp32) under the keys peft / the reference module tree use.
+    _PEFT = "nnmodule.base_model.model.model.layers.%d.%s.%s.lora_%s.default.weight"
+    _PROJ = (("self_attn", "q_proj", "Acat_qkv", 0, "Bt_q"), ("self_attn", "k_proj", "Acat_qkv", 1, "Bt_k"),
+             ("self_attn", "v_proj", "Acat_qkv", 2, "Bt_v"), ("self_attn", "o_proj", "A_o", 0, "Bt_o"),
+             ("mlp", "gate_proj", "Acat_gu", 0, "Bt_g"), ("mlp", "up_proj", "Acat_gu", 1, "Bt_u"),
+             ("mlp", "down_proj", "A_d", 0, "Bt_d"))
+    _HEAD = (("ridge_layer.linear.weight", "ridge_w"), ("ridge_layer.linear.bias", "ridge_b"),
+             ("layer_norm1.weight", "ln1_w"), ("layer_norm1.bias", "ln1_b"),
+             ("layer_norm2.weight", "ln2_w"), ("layer_norm2.bias", "ln2_b"))
+
+    def _adapter_views(self):
+        """(checkpoint key, fp32 view of the flat master, transposed?) for every trainable tensor."""
+        T, r = self.engine.T, self.model_config.lora_r
+        out = []
+        for l in range(T.lora_layers):
+            for blk, proj, a_name, a_idx, b_name in self._PROJ:
+                a = T.p("layers.%d.%s" % (l, a_name))[a_idx * r:(a_idx + 1) * r]
+                out.append((self._PEFT % (l, blk, proj, "A"), a, False))
+                out.append((self._PEFT % (l, blk, proj, "B"), T.p("layers.%d.%s" % (l, b_name)), True))   # stored [r, N]
+        out += [(k, T.p(n), False) for k, n in self._HEAD]
+        return out
+
+    def adapter_state_dict(self):
+        return {k: (v.t() if tr else v).detach().clone().contiguous().cpu() for k, v, tr in self._adapter_views()}
+
+    def load_adapter_state_dict(self, sd, strict=True):
+        missing = []
+        for k, v, tr in self._adapter_views():
+            if k not in sd:
+                missing.append(k)
+                continue
+            src = sd[k].to(device=v.device, dtype=torch.float32)
+            v.copy_(src.t() if tr else src)
+        if strict and missing:
+            raise KeyError("adapter checkpoint is missing %d keys, e.g. %s" % (len(missing), missing[0]))
+        self.engine.T.sync_working()
+        return missing
+
+    def save_adapters(self, path):
+        torch.save({"state_dict": self.adapter_state_dict(), "step_count": self.engine.T.step_count,
+                    "adam_m": self.engine.T.m.cpu(), "adam_v": self.engine.T.v.cpu()}, path)
+
+    def load_adapters(self, path, load_optimizer=True):
+        ck = torch.load(path, map_location="cpu")
+        self.load_adapter_state_dict(ck["state_dict"])
+        if load_optimizer and "adam_m" in ck:
+            T = self.engine.T
+            T.m.copy_(ck["adam_m"]); T.v.copy_(ck["adam_v"]); T.step_count = int(ck["step_count"])
+
+    def on_save_checkpoint(self, checkpoint):           # Lightning hook: trainer.save_checkpoint(...) (train.py:58)
+        checkpoint["state_dict"] = self.adapter_state_dict()
+
     # ------------------------------------------------------------------ helpers
     def make_weight_mask(self, pad_vals, vis_weights, lang_weights, lang_len, max_len):
         mc = self.model_config

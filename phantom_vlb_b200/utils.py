@@ -59,13 +59,25 @@ def pearson_columns(preds, targets, group=None):
 
 
 class LogValAccuracyCallback(Callback):
+    def __init__(self, csv_dir=None):
+        """csv_dir: when set, every validation epoch also appends one row to <csv_dir>/metrics.csv with the reference's
+        column names, so make_acc_brainmaps.py (and postprocessing.make_brainmaps) can read it without Lightning's logger."""
+        super().__init__()
+        self.csv_writer = None
+        if csv_dir is not None:
+            from .postprocessing import MetricsCSVWriter
+            self.csv_writer = MetricsCSVWriter(csv_dir)
+
     def on_validation_epoch_start(self, trainer, pl_module):
         self.val_actual = []
         self.val_pred = []
+        self.val_loss = []
 
     def on_validation_batch_end(self, trainer, pl_module, outputs, batch, batch_idx, dataloader_idx=0):
         self.val_actual.append(outputs["brain_vals"])
         self.val_pred.append(outputs["brain_preds"])
+        if "loss" in outputs:
+            self.val_loss.append(outputs["loss"].detach().clone())
 
     def on_validation_epoch_end(self, trainer, pl_module):
         all_vals = torch.cat(self.val_actual, dim=0)
@@ -75,3 +87,6 @@ class LogValAccuracyCallback(Callback):
         pl_module.log_dict({f"val_corr_ROI_{i:0{6}}": float(host[i]) for i in range(pl_module.config.num_target)})
         pl_module.log("val_corr_avg", float(np.mean(host)))
         self.last_correlations = host
+        if getattr(self, "csv_writer", None) is not None:            # columnar metrics.csv (postprocessing.MetricsCSVWriter)
+            loss = torch.stack([v.float().mean() for v in self.val_loss]).mean().item() if getattr(self, "val_loss", None) else float("nan")
+            self.csv_writer.log_validation(getattr(trainer, "current_epoch", 0), getattr(trainer, "global_step", 0), loss, host)
