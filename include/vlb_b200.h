@@ -74,6 +74,11 @@ int vlb_swiglu_bwd(const void* gu, const void* dact, void* dgu, long long M, int
  * prepare_inputs_labels_for_multimodal (videollama2_arch.py:161-263), batch["language"].long()
  * (src/litmodule/videollama2_vlb_litmodule.py:269) and make_weight_mask (litmodule.py:178-203). */
 int vlb_patch_im2col(const void* pixels_f32, void* cols, long long N, int img, int patch, int kpad, void* stream);
+/* uint8 frames [N,3,img,img]: CLIPImageProcessor rescale (1/255) + normalise ((x-mean)/std, HOST pointers to 3 floats
+ * each) fused into the gather -- the arithmetic src/preprocessing/videollama2_vlb_extractfeatures.py:344-350 does on the
+ * CPU before writing fp32 pixels to HDF5. */
+int vlb_patch_im2col_u8(const void* pixels_u8, void* cols, long long N, int img, int patch, int kpad,
+                        const float* mean3, const float* std3, void* stream);
 int vlb_clip_embed(const void* patch, const void* cls, const void* pos, const void* lnw, const void* lnb,
                    void* out, long long N, int T, int H, float eps, void* stream);
 int vlb_drop_cls(const void* in, void* out, long long N, int T, int H, void* stream);

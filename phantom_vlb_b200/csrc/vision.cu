@@ -34,6 +34,30 @@ __global__ void patch_im2col_kernel(const float* __restrict__ pix, bf16* __restr
     }
 }
 
+// uint8 frames: the CLIPImageProcessor arithmetic the reference runs on the CPU before storing fp32 pixels
+// (rescale by 1/255, then (x - mean[c]) / std[c]; extractfeatures.py:344-350 via processor.preprocess) is applied in the
+// gather itself, with the same fp32 operation order (round-to-nearest mul, sub, div: bit-identical to the stored fp32
+// pixels), so a clip travels as 2.7 MB of bytes instead of 10.8 MB of floats.
+struct ClipNorm { float mean[3]; float std[3]; };
+__global__ void patch_im2col_u8_kernel(const uint8_t* __restrict__ pix, bf16* __restrict__ cols, long long N, int IMG, int P,
+                                       int G, int KP, ClipNorm nm) {
+    const int K = 3 * P * P;
+    const long long total = N * G * G * (long long)KP;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int k = (int)(i % KP);
+        const long long pr = i / KP;
+        float v = 0.f;
+        if (k < K) {
+            const int c = k / (P * P), ky = (k / P) % P, kx = k % P;
+            const int gx = (int)(pr % G), gy = (int)((pr / G) % G);
+            const long long n = pr / (G * G);
+            const float raw = (float)pix[((n * 3 + c) * IMG + gy * P + ky) * (long long)IMG + gx * P + kx];
+            v = __fdiv_rn(__fsub_rn(__fmul_rn(raw, 0.00392156862745098f), nm.mean[c]), nm.std[c]);
+        }
+        cols[i] = f2bf(v);
+    }
+}
+
 // hidden0[n, t, :] = LN( (t == 0 ? cls : patch[n, t-1, :]) + pos[t, :] ); one CTA (128 thr) per token; H % 8 == 0, H <= 1024*?
 template <int MAXV>
 __global__ void __launch_bounds__(128) clip_embed_kernel(const bf16* __restrict__ patch, const bf16* __restrict__ cls,
@@ -260,6 +284,19 @@ extern "C" int vlb_patch_im2col(const void* pixels_f32, void* cols, long long N,
     patch_im2col_kernel<<<grid_for(N * G * G * (long long)kpad, 256), 256, 0, (cudaStream_t)stream>>>(
         (const float*)pixels_f32, (bf16*)cols, N, img, patch, G, kpad);
     return check_launch("patch_im2col");
+}
+
+extern "C" int vlb_patch_im2col_u8(const void* pixels_u8, void* cols, long long N, int img, int patch, int kpad,
+                                   const float* mean3, const float* std3, void* stream) {
+    VLB_REQUIRE(img % patch == 0 && kpad >= 3 * patch * patch && kpad % 8 == 0, "patch_im2col_u8: img=%d patch=%d kpad=%d",
+                img, patch, kpad);
+    VLB_REQUIRE(mean3 != nullptr && std3 != nullptr, "patch_im2col_u8: mean/std (3 host floats each) are required");
+    ClipNorm nm;
+    for (int c = 0; c < 3; ++c) { nm.mean[c] = mean3[c]; nm.std[c] = std3[c]; }
+    const int G = img / patch;
+    patch_im2col_u8_kernel<<<grid_for(N * G * G * (long long)kpad, 256), 256, 0, (cudaStream_t)stream>>>(
+        (const uint8_t*)pixels_u8, (bf16*)cols, N, img, patch, G, kpad, nm);
+    return check_launch("patch_im2col_u8");
 }
 
 extern "C" int vlb_clip_embed(const void* patch, const void* cls, const void* pos, const void* lnw, const void* lnb,

@@ -61,7 +61,7 @@ class Engine:
 
     # ------------------------------------------------------------------ vision tower (frozen, forward only)
     def vit_forward(self, pixels):
-        """pixels fp32 [N, 3, H, W] -> patch features bf16 [N*G*G, Hv] (hidden_states[-2][:, 1:], encoder.py:31-53)."""
+        """pixels fp32 (normalised) or uint8 (raw) [N, 3, H, W] -> patch features bf16 [N*G*G, Hv] (hidden_states[-2][:, 1:], encoder.py:31-53)."""
         cfg, W = self.cfg, self.W
         N = pixels.shape[0]
         G2, Hv, T = cfg.grid ** 2, cfg.vit_hidden, cfg.grid ** 2 + 1
@@ -251,7 +251,7 @@ class Engine:
         cfg = self.cfg
         vision = batch["vision"]
         B, Tn = vision.shape[0], vision.shape[1]
-        assert Tn == cfg.num_frames and vision.dtype == torch.float32
+        assert Tn == cfg.num_frames and vision.dtype in (torch.float32, torch.uint8)     # uint8: raw frames (f-1)
         assert batch["language"].shape[1] == cfg.l_text, "text length must be max_len - n_vis + 1 (litmodule.py:180-181)"
         feats = self.vit_forward(vision.reshape(B * Tn, 3, cfg.image_size, cfg.image_size))
         vis = self.stc_forward(feats, B)

@@ -136,12 +136,23 @@ def swiglu_bwd(gu, dact, out=None):
 
 
 # ------------------------------------------------------------------------------------------------ vision / splice
-def patch_im2col(pixels, patch, kpad, out=None):
+CLIP_MEAN = (0.48145466, 0.4578275, 0.40821073)      # transformers OPENAI_CLIP_MEAN / OPENAI_CLIP_STD (CLIPImageProcessor)
+CLIP_STD = (0.26862954, 0.26130258, 0.27577711)
+
+
+def patch_im2col(pixels, patch, kpad, out=None, mean=CLIP_MEAN, std=CLIP_STD):
+    """pixels [N,3,H,W]: fp32 CLIP-normalised values (the reference batch contract) or raw uint8 frames, in which case the
+    rescale + normalise of CLIPImageProcessor is fused into the gather."""
     N, C, H, W = pixels.shape
-    assert C == 3 and H == W and pixels.dtype == torch.float32 and pixels.is_contiguous()
+    assert C == 3 and H == W and pixels.is_contiguous() and pixels.dtype in (torch.float32, torch.uint8)
     G = H // patch
     out = torch.empty((N * G * G, kpad), device=pixels.device, dtype=torch.bfloat16) if out is None else out
-    _l.call("vlb_patch_im2col", _l.ptr(pixels), _l.ptr(out), N, H, patch, kpad, _st())
+    if pixels.dtype == torch.uint8:
+        import ctypes
+        m3, s3 = (ctypes.c_float * 3)(*mean), (ctypes.c_float * 3)(*std)
+        _l.call("vlb_patch_im2col_u8", _l.ptr(pixels), _l.ptr(out), N, H, patch, kpad, m3, s3, _st())
+    else:
+        _l.call("vlb_patch_im2col", _l.ptr(pixels), _l.ptr(out), N, H, patch, kpad, _st())
     return out
 
 

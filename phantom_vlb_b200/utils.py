@@ -31,6 +31,16 @@ def get_hrf_weight(time_diff: float) -> float:
     return h / 0.1758
 
 
+def hrf_weights(time_diffs):
+    """Vectorised get_hrf_weight over an array of lags (seconds): one numpy expression instead of one nilearn
+    compute_regressor call per visual / language token (lazyloading.py:113-115, 135-137 -- the per-token Python loop the
+    reference runs for every sample). Returns float64 like the reference's weight arrays."""
+    t = np.asarray(time_diffs, dtype=np.float64)
+    tp = np.where(t > 0, t, 1.0)
+    h = (tp ** 5 * np.exp(-tp) / math.gamma(6.0)) - (tp ** 15 * np.exp(-tp) / math.gamma(16.0)) / 6.0
+    return np.where(t > 0, h / 0.1758, 0.0)
+
+
 class HRFConvolveLayer(torch.nn.Module):
     """Weighted sum of token embeddings by HRF weight: einsum('bse,bs->be'). Fused into vlb_hrf_pool_fwd."""
 

@@ -144,3 +144,19 @@ def test_row_kernels_match_fp32_formulas():
     assert (q.float().view(3, S, nh, D) - exp).abs().max().item() < 4e-2
     ops.rope_(q, cos, sin, S, nh, D, inverse=True)
     assert (q.float() - q0.float()).abs().max().item() < 6e-2
+
+
+def test_uint8_frames_normalised_in_gather_bit_exact():
+    """f-1: raw uint8 frames + fused CLIP rescale/normalise give the same im2col matrix, bit for bit, as the reference
+    route (CLIPImageProcessor arithmetic in fp32 on the host, fp32 pixels in the batch, .to(bf16) on the device)."""
+    from phantom_vlb_b200 import ops
+    g = torch.Generator().manual_seed(8)
+    frames = torch.randint(0, 256, (3, 3, 56, 56), generator=g, dtype=torch.uint8)
+    mean = torch.tensor(ops.CLIP_MEAN, dtype=torch.float32).view(1, 3, 1, 1)
+    std = torch.tensor(ops.CLIP_STD, dtype=torch.float32).view(1, 3, 1, 1)
+    ref_pixels = ((frames.float() * (1.0 / 255.0)) - mean) / std          # rescale then normalise, fp32 (image_processing_clip)
+    kpad = (3 * 14 * 14 + 7) // 8 * 8
+    a = ops.patch_im2col(ref_pixels.cuda().contiguous(), 14, kpad)
+    b = ops.patch_im2col(frames.cuda().contiguous(), 14, kpad)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)

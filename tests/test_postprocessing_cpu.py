@@ -42,3 +42,12 @@ def test_nifti1_header_and_payload(tmp_path):
     assert struct.unpack_from("<4f", raw, 280) == (2.0, 0.0, 0.0, -90.0)
     data = np.frombuffer(raw, dtype="<f4", offset=352).reshape(4, 3, 2).transpose(2, 1, 0)    # x fastest on disk
     assert np.array_equal(data, vol)
+
+
+def test_vectorised_hrf_weights_match_scalar():
+    from phantom_vlb_b200.utils import get_hrf_weight, hrf_weights
+    lags = np.concatenate([1.49 * (5.5 - np.arange(0, 3 + 0.75, 0.75)), [-1.0, 0.0, 0.3, 30.0]])     # visual-token lags
+    w = hrf_weights(lags)
+    assert w.dtype == np.float64 and w.shape == lags.shape
+    assert np.allclose(w, [get_hrf_weight(float(t)) for t in lags], rtol=1e-12, atol=0)
+    assert w[-4] == 0.0 and w[-3] == 0.0 and abs(hrf_weights([5.0])[0] - 1.0) < 0.05             # peak-normalised near 5 s
