@@ -195,9 +195,10 @@ def run_ours(args):
     peak_tf, peak_bw, peak_src = peaks()
     achieved = sum(f for _, f in big) / (sum(t for t, _ in big) / 1e3) / 1e12
     step_ms = ms / K
-    roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (decoder/ViT/STC GEMMs with fused LoRA k-block)",
+    roofline = {"bound": "tensor", "kernel": "gemm2_tcgen05_kernel (cta_group::2 pair tiles 256x256) / gemm_tcgen05_kernel: decoder, ViT and STC GEMMs with the fused LoRA k-block",
                 "achieved": round(achieved, 1), "peak": peak_tf, "unit": "TFLOP/s", "frac": round(achieved / peak_tf, 4),
                 "traffic": None, "peak_source": peak_src, "launches_timed": len(big),
+                "how": "one extra instrumented step: CUDA events around every GEMM launch on the launching stream; achieved = sum of algorithmic 2*M*N*(K+K2) over launches with M,N >= 1024 / sum of their times. The host-side event overhead leaves short idle gaps between launches, so the power-capped SM clock can sit slightly higher than inside the plain timed step",
                 "gemm_share_of_step": round(g_ms / step_ms, 4), "all_gemm_tflops": round(g_fl / (g_ms / 1e3) / 1e12, 1),
                 "step_tflops": round(B * TF_FULL / (step_ms / 1e3), 1)}
     res = None

@@ -1,0 +1,202 @@
+// CTA-pair (cta_group::2) variant of the tcgen05 GEMM for the big decoder / ViT / STC linears (bf16 output, K-major A).
+// Included by gemm_sm100.cu after the single-CTA kernel (shares GemmParams, tile_coords, BM, BK, CD_STAGE_BYTES).
+//
+// A cluster of two CTAs (one TPC) owns a 256 x 256 output tile: CTA r holds rows [m0 + 128 r, +128) of A and columns
+// [n0 + 128 r, +128) of B in its shared memory, so each k-block costs 32 KB of smem traffic per SM instead of 48 KB and
+// the ring is 6 deep instead of 4. The leader's single MMA thread issues tcgen05.mma.cta_group::2 (M = 256, N = 256,
+// K = 16); the fp32 accumulator rows land in each CTA's own TMEM (2 stages x 256 columns) and each CTA runs its own
+// epilogue on its 128 rows. Barrier protocol:
+//   full[s]   (leader only)  1 arrival (leader producer's expect_tx of BOTH CTAs' bytes) + TMA complete_tx from both CTAs
+//   empty[s]  (both)         tcgen05.commit multicast from the leader's MMA thread
+//   tfull[a]  (both)         tcgen05.commit multicast
+//   tempty[a] (leader only)  256 arrivals: the 128 epilogue threads of each CTA (remote mbarrier.arrive from the peer)
+#pragma once
+
+namespace vlb {
+
+constexpr int G2_BN = 256;                 // pair tile columns
+constexpr int G2_HALF_N = G2_BN / 2;       // B columns held by each CTA
+constexpr int G2_A_BYTES = BM * BK * 2;    // 16 KB
+constexpr int G2_B_BYTES = G2_HALF_N * BK * 2;   // 16 KB
+constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_B_BYTES;
+constexpr int G2_STAGES = SMEM_AB_BYTES / G2_STAGE_BYTES;    // 6
+constexpr int G2_SMEM_BYTES = G2_STAGES * G2_STAGE_BYTES + 2 * CD_STAGE_BYTES + 1024 + 256;
+constexpr int G2_TMEM_COLS = 512;
+
+template <bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm2_tcgen05_kernel(const GemmParams p,
+                     const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                     const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                     const __grid_constant__ CUtensorMap tmC) {
+    constexpr int STAGES = G2_STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES * G2_A_BYTES;
+    uint8_t* smem_cd = smem + STAGES * G2_STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_cd + 2 * CD_STAGE_BYTES);
+    uint64_t* full_bar = bars;                    // [STAGES]
+    uint64_t* empty_bar = bars + STAGES;          // [STAGES]
+    uint64_t* tfull_bar = bars + 2 * STAGES;      // [2]
+    uint64_t* tempty_bar = bars + 2 * STAGES + 2; // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    const int nk = p.nk1 + p.nk2;
+    const int num_tiles = p.mt * p.nt;            // p.mt counts 256-row blocks here
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA1); tma_prefetch_desc(&tmB1); tma_prefetch_desc(&tmC);
+        if (p.nk2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 256); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc_2sm<G2_TMEM_COLS>(tmem_ptr);
+    tc_fence_before();
+    cluster_sync_all();                            // barriers of BOTH CTAs are initialised before any remote arrive / TMA
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer (both CTAs)
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = pair; t < num_tiles; t += num_pairs) {
+                int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb);
+                const int m0 = mb * (2 * BM) + (int)rank * BM, n0 = nb * G2_BN + (int)rank * G2_HALF_N;
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * G2_STAGE_BYTES);
+                    const bool second = kb >= p.nk1;
+                    const CUtensorMap* ta = second ? &tmA2 : &tmA1;
+                    const CUtensorMap* tb = second ? &tmB2 : &tmB1;
+                    const int k0 = (second ? kb - p.nk1 : kb) * BK;
+                    uint8_t* sa = smem_a + stage * G2_A_BYTES;
+                    uint8_t* sb = smem_b + stage * G2_B_BYTES;
+                    tma_load_2d_2sm(ta, &full_bar[stage], sa, k0, m0);
+                    if constexpr (!B_MN) {
+                        tma_load_2d_2sm(tb, &full_bar[stage], sb, k0, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < G2_HALF_N / 64; ++j)
+                            tma_load_2d_2sm(tb, &full_bar[stage], sb + j * (BK * 128), n0 + j * 64, k0);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (leader CTA, one thread)
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(2 * BM, G2_BN, false, B_MN);
+            constexpr uint32_t LBO = BK * 128;
+            constexpr uint32_t KSTEP_B = B_MN ? (16 * 128) : 32;
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(&tempty_bar[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * G2_BN;
+                for (int kb = 0; kb < nk; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem_a + stage * G2_A_BYTES);
+                    const uint32_t b_addr = smem_u32(smem_b + stage * G2_B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t ad = make_smem_desc(a_addr + k * 32, 0, 1024);
+                        const uint64_t bd = make_smem_desc(b_addr + k * KSTEP_B, B_MN ? LBO : 0, 1024);
+                        umma_bf16_2sm(d_tmem, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit_2sm(&empty_bar[stage]);
+                    if (kb == nk - 1) umma_commit_2sm(&tfull_bar[as]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ epilogue (128 threads per CTA, own 128 rows)
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        int it = 0;
+        uint32_t cd_idx = 0;
+        const bool issuer = (warp == 4 && lane == 0);
+        for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+            int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb);
+            const int m0 = mb * (2 * BM) + (int)rank * BM, n0 = nb * G2_BN;
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            mbar_wait(&tfull_bar[as], aphase);
+            tc_fence_after();
+            const int m = m0 + row;
+            const bool m_ok = m < p.M;
+#pragma unroll 1
+            for (int s = 0; s < G2_BN / 64; ++s, ++cd_idx) {
+                uint8_t* cd = smem_cd + (cd_idx & 1) * CD_STAGE_BYTES;
+                if (issuer) tma_store_wait_read<1>();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t r[32];
+                    const int c0 = s * 64 + h * 32;
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + c0), r);
+                    tmem_ld_wait();
+                    const int n = n0 + c0;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        float v[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
+                        const int nn = n + c * 8;
+                        const bool n_ok = nn < p.N;
+                        if (p.bias != nullptr && n_ok) {
+                            float b[8]; load8(p.bias + nn, b);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] += b[j];
+                        }
+                        if (p.act != ACT_NONE) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
+                        }
+                        if (p.residual != nullptr && m_ok && n_ok) {
+                            float rr[8]; load8(p.residual + (size_t)m * p.ldr + nn, rr);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = bf2f(f2bf(v[j])) + rr[j];
+                        }
+                        uint4 u;
+                        u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);
+                        u.z = pack_bf16(v[4], v[5]); u.w = pack_bf16(v[6], v[7]);
+                        const int chunk = h * 4 + c;
+                        *reinterpret_cast<uint4*>(cd + row * 128 + ((chunk ^ (row & 7)) << 4)) = u;
+                    }
+                }
+                if (s == G2_BN / 64 - 1) {                  // this CTA's TMEM reads of the accumulator stage are done
+                    tc_fence_before();
+                    mbar_arrive_cluster(&tempty_bar[as], 0);
+                }
+                fence_proxy_async_smem();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (issuer) {
+                    tma_store_2d(&tmC, cd, n0 + s * 64, m0);
+                    tma_store_commit();
+                }
+            }
+        }
+        if (issuer) tma_store_wait_all<0>();
+    }
+
+    tc_fence_before();
+    cluster_sync_all();       // the peer's smem / TMEM stay alive until the leader's last MMA and remote arrive have landed
+    if (warp == 2) { tc_fence_after(); tmem_dealloc_2sm<G2_TMEM_COLS>(tmem_base); }
+}
+
+}  // namespace vlb

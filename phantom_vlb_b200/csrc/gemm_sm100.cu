@@ -20,6 +20,7 @@
 #include <unordered_map>
 #include <string>
 #include <string.h>
+#include <stdlib.h>
 
 namespace vlb {
 
@@ -51,10 +52,10 @@ struct GemmParams {
     int ldc32;
     int accum_f32;          // c_f32 += result instead of =
     int splits;             // split-K factor (fp32 accumulate outputs only): partial tiles are red.add'ed
+    int group_m;            // M-blocks swept together before moving to the next N-block (L2 residency of the A panel)
 };
 
-__device__ __forceinline__ void tile_coords(int t, int mt, int nt, int& mb, int& nb) {
-    constexpr int GROUP_M = 8;
+__device__ __forceinline__ void tile_coords(int t, int mt, int nt, int GROUP_M, int& mb, int& nb) {
     const int per_group = GROUP_M * nt;
     const int g = t / per_group;
     const int first_m = g * GROUP_M;
@@ -118,7 +119,7 @@ gemm_tcgen05_kernel(const GemmParams p,
             int stage = 0; uint32_t phase = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
                 int tile, kb0, kb1; split_range(t, p.splits, nk, tile, kb0, kb1);
-                int mb, nb; tile_coords(tile, p.mt, p.nt, mb, nb);
+                int mb, nb; tile_coords(tile, p.mt, p.nt, p.group_m, mb, nb);
                 const int m0 = mb * BM, n0 = nb * BN;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -189,7 +190,7 @@ gemm_tcgen05_kernel(const GemmParams p,
         uint32_t cd_idx = 0;
         const bool issuer = (warp == 4 && lane == 0);
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-            int mb, nb; tile_coords(t / p.splits, p.mt, p.nt, mb, nb);
+            int mb, nb; tile_coords(t / p.splits, p.mt, p.nt, p.group_m, mb, nb);
             const int m0 = mb * BM, n0 = nb * BN;
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
@@ -287,6 +288,12 @@ gemm_tcgen05_kernel(const GemmParams p,
     __syncthreads();
     if (warp == 2) { tc_fence_after(); tmem_dealloc<Cfg::TMEM_COLS>(tmem_base); }
 }
+
+}  // namespace vlb
+
+#include "gemm2_kernel.cuh"
+
+namespace vlb {
 
 // ------------------------------------------------------------------------------------------------ host side
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -424,6 +431,8 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     p.mt = ceil_div(a.M, BM); p.nt = ceil_div(a.N, BN);
     p.c_f32 = a.c_is_f32 ? reinterpret_cast<float*>(a.C) : nullptr;
     p.ldc32 = a.ldc; p.accum_f32 = a.accum;
+    p.group_m = 8;
+    { const char* g = getenv("VLB_GEMM_GROUP_M"); if (g && atoi(g) > 0) p.group_m = atoi(g); }
     // split-K: gradient GEMMs contract over all tokens into a tiny [r, N] output; without it only mt*nt (< 148) CTAs
     // stream the activations. Partial tiles are red.add'ed, so the output must already hold the value to add to.
     p.splits = 1;
@@ -449,6 +458,57 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     return check_launch("gemm_tcgen05_kernel");
 }
 
+// CTA-pair launch: 256 x 256 tiles, bf16 output, K-major A (the decoder / ViT / STC linears and their dX GEMMs).
+template <bool B_MN>
+static int launch_gemm2(const GemmArgs& a, cudaStream_t stream) {
+    CUtensorMap tA1, tB1, tA2, tB2, tC;
+    int rc;
+    if ((rc = make_tmap(&tA1, a.A1, a.K1, a.M, a.lda1, BK, BM))) return rc;
+    if (!B_MN) rc = make_tmap(&tB1, a.B1, a.K1, a.N, a.ldb1, BK, G2_HALF_N);
+    else       rc = make_tmap(&tB1, a.B1, a.N, a.K1, a.ldb1, 64, BK);
+    if (rc) return rc;
+    if (a.K2 > 0) {
+        if ((rc = make_tmap(&tA2, a.A2, a.K2, a.M, a.lda2, BK, BM))) return rc;
+        if (!B_MN) rc = make_tmap(&tB2, a.B2, a.K2, a.N, a.ldb2, BK, G2_HALF_N);
+        else       rc = make_tmap(&tB2, a.B2, a.N, a.K2, a.ldb2, 64, BK);
+        if (rc) return rc;
+    } else { tA2 = tA1; tB2 = tB1; }
+    if ((rc = make_tmap(&tC, a.C, a.N, a.M, a.ldc, 64, BM))) return rc;
+    GemmParams p;
+    p.M = a.M; p.N = a.N;
+    p.nk1 = ceil_div(a.K1, BK); p.nk2 = a.K2 > 0 ? ceil_div(a.K2, BK) : 0;
+    p.alpha = a.alpha;
+    p.bias = reinterpret_cast<const bf16*>(a.bias);
+    p.residual = reinterpret_cast<const bf16*>(a.residual);
+    p.ldr = a.ldr; p.act = a.act;
+    p.mt = ceil_div(a.M, 2 * BM); p.nt = ceil_div(a.N, G2_BN);
+    p.c_f32 = nullptr; p.ldc32 = 0; p.accum_f32 = 0; p.splits = 1;
+    // M-blocks (256 rows) swept together before moving to the next N-block: the A panel (group x 256 x K) stays in L2
+    // while B streams past it. Measured sustained at M=16384: K=4096 shapes +1.5..3 % at 16, K >= 14336 shapes best at 8.
+    p.group_m = a.K1 <= 8192 ? 16 : 8;
+    { const char* g = getenv("VLB_GEMM_GROUP_M"); if (g && atoi(g) > 0) p.group_m = atoi(g); }
+    auto kern = gemm2_tcgen05_kernel<B_MN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES);
+        VLB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(gemm2 smem=%d): %s", G2_SMEM_BYTES, cudaGetErrorString(e));
+        attr_set = true;
+    }
+    int pairs = p.mt * p.nt;
+    int cap = (a.max_ctas > 0 ? a.max_ctas : num_sms()) / 2;
+    if (pairs > cap) pairs = cap;
+    if (pairs < 1) pairs = 1;
+    kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC);
+    return check_launch("gemm2_tcgen05_kernel");
+}
+
+static bool use_pair_kernel(const GemmArgs& a) {
+    static int mode = -1;                           // VLB_GEMM_2CTA=0 forces the single-CTA kernel (A/B comparisons)
+    if (mode < 0) { const char* e = getenv("VLB_GEMM_2CTA"); mode = (e && atoi(e) == 0) ? 0 : 1; }
+    return mode == 1 && !a.a_mn && !a.c_is_f32 && a.M >= 2 * BM && a.N >= G2_BN &&
+           (long long)ceil_div(a.M, 2 * BM) * ceil_div(a.N, G2_BN) >= num_sms() / 2;
+}
+
 template <int BN>
 static int dispatch_major(const GemmArgs& a, cudaStream_t s) {
     if (!a.a_mn && !a.b_mn) return launch_gemm<BN, false, false>(a, s);
@@ -467,6 +527,7 @@ int gemm_dispatch(const GemmArgs& a, int block_n, cudaStream_t s) {
         long long tiles = (long long)ceil_div(a.M, BM) * ceil_div(a.N, 256);
         if (block_n == 0 && tiles < num_sms()) bn = 128;
     }
+    if (bn == 256 && use_pair_kernel(a)) return a.b_mn ? launch_gemm2<true>(a, s) : launch_gemm2<false>(a, s);
     switch (bn) {
         case 256: return dispatch_major<256>(a, s);
         case 128: return dispatch_major<128>(a, s);

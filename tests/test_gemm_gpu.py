@@ -112,3 +112,28 @@ def test_gemm_split_k_needs_accumulate():
     b = torch.zeros(256, 128, device="cuda").bfloat16()
     with pytest.raises(RuntimeError):
         ops.gemm(a, b, a_mn=True, b_mn=True, out_f32=True, accumulate=False, split_k=4)
+
+
+@pytest.mark.parametrize("b_mn", [False, True])
+@pytest.mark.parametrize("M,N,K,R", [(4096, 4096, 512, 0), (4096 + 200, 5120, 320, 48), (16384, 2304, 192, 16), (2560, 8192, 1088, 32)])
+def test_gemm_cta_pair_kernel(M, N, K, R, b_mn):
+    """Shapes with >= 74 tiles of 256 x 256 take the cta_group::2 kernel (gemm2_kernel.cuh): ragged M (the peer CTA's rows
+    partly / fully out of range), fused LoRA k-block (K2 < 64: zero-filled by TMA), bias + activation + residual epilogue."""
+    from phantom_vlb_b200 import ops
+    torch.manual_seed(M + N + K + R)
+    dev = "cuda"
+    a = torch.randn(M, K, device=dev).bfloat16()
+    b = (torch.randn((K, N) if b_mn else (N, K), device=dev) * 0.05).bfloat16()
+    a2 = b2 = None
+    if R:
+        a2 = torch.randn(M, R, device=dev).bfloat16()
+        b2 = (torch.randn((R, N) if b_mn else (N, R), device=dev) * 0.1).bfloat16()
+    bias = torch.randn(N, device=dev).bfloat16()
+    res = torch.randn(M, N, device=dev).bfloat16()
+    out = ops.gemm(a, b, a2=a2, b2=b2, alpha=0.5, bias=bias, residual=res, act=3, b_mn=b_mn)
+    torch.cuda.synchronize()
+    _close(out, _ref(a, b, a2, b2, 0.5, bias, res, 3, False, b_mn))
+    # and the plain product, repeated to cover the accumulator double-buffer / ring wrap-around across many tiles
+    out2 = ops.gemm(a, b, b_mn=b_mn)
+    torch.cuda.synchronize()
+    _close(out2, _ref(a, b, None, None, 1.0, None, None, 0, False, b_mn))
