@@ -29,8 +29,8 @@ template <int D> struct AttCfg {
     static constexpr int OFF_P = OFF_V + 2 * KV_BYTES;
     static constexpr int OFF_BAR = OFF_P + P_BYTES;
     static constexpr int SMEM_BYTES = OFF_BAR + 128;          // + barriers; two CTAs fit one SM
-    static constexpr int TMEM_COLS = (ATT_BN + D <= 128) ? 128 : 256;
-    static constexpr int O_COL = ATT_BN;                      // S at column 0, O after it
+    static constexpr int TMEM_COLS = 256;                     // two S buffers (64 columns each) + O (D columns); x2 CTAs = 512
+    static constexpr int O_COL = 2 * ATT_BN;                  // S0 at column 0, S1 at 64, O after them
 };
 
 struct AttParams {
@@ -59,10 +59,10 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
     uint64_t* k_empty = bars + 3;       // [2]
     uint64_t* v_full = bars + 5;        // [2]
     uint64_t* v_empty = bars + 7;       // [2]
-    uint64_t* s_full = bars + 9;        // [1]
-    uint64_t* p_ready = bars + 10;      // [1] count 128
-    uint64_t* pv_done = bars + 11;      // [1]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+    uint64_t* s_full = bars + 9;        // [2] one per S buffer
+    uint64_t* p_ready = bars + 11;      // [1] count 128
+    uint64_t* pv_done = bars + 12;      // [1]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nqb = gridDim.x;
@@ -79,7 +79,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
     if (warp == 1 && lane == 0) {
         mbar_init(q_full, 1);
         for (int i = 0; i < 2; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
-        mbar_init(s_full, 1); mbar_init(p_ready, 128); mbar_init(pv_done, 1);
+        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(p_ready, 128); mbar_init(pv_done, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
@@ -121,19 +121,21 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 for (int k = 0; k < D / 16; ++k) {
                     const uint32_t off_q = (k >> 2) * (ATT_BM * 128) + (k & 3) * 32;
                     const uint32_t off_k = (k >> 2) * (ATT_BN * 128) + (k & 3) * 32;
-                    umma_bf16(tS, make_smem_desc(qa + off_q, 0, 1024), make_smem_desc(ka + off_k, 0, 1024), idesc_qk,
-                              k > 0 ? 1u : 0u);
+                    umma_bf16(tS + (uint32_t)(st * ATT_BN), make_smem_desc(qa + off_q, 0, 1024),
+                              make_smem_desc(ka + off_k, 0, 1024), idesc_qk, k > 0 ? 1u : 0u);
                 }
                 umma_commit(&k_empty[st]);
-                umma_commit(s_full);
+                umma_commit(&s_full[st]);
             };
+            // S is double-buffered in TMEM and issued two key blocks ahead, so the tensor pipe computes S(j+1) while the
+            // softmax threads are still working on S(j); PV(j) (on the critical path to the next P write) goes first.
             mbar_wait(q_full, 0);
             issue_qk(0);
+            if (nblk > 1) issue_qk(1);
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1;
-                mbar_wait(p_ready, j & 1);
+                mbar_wait(p_ready, j & 1);                // P(j) in smem; S buffer j & 1 drained
                 tc_fence_after();
-                if (j + 1 < nblk) issue_qk(j + 1);
                 mbar_wait(&v_full[st], (j >> 1) & 1);
                 tc_fence_after();
                 const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * Cfg::KV_BYTES);
@@ -145,6 +147,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 }
                 umma_commit(&v_empty[st]);
                 umma_commit(pv_done);
+                if (j + 2 < nblk) issue_qk(j + 2);
             }
         }
     } else if (warp >= 4) {
@@ -155,11 +158,11 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
         const int qrow = q0 + row;
         float m_used = -INFINITY, l = 0.f;
         for (int j = 0; j < nblk; ++j) {
-            mbar_wait(s_full, j & 1);
+            mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             tc_fence_after();
             uint32_t r0[32], r1[32];
-            tmem_ld32(tS, r0);
-            tmem_ld32(tS + 32, r1);
+            tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN), r0);
+            tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN) + 32, r1);
             tmem_ld_wait();
             float s[64];
 #pragma unroll
