@@ -88,7 +88,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         for (int j = 0; j < G2_HALF_N / 64; ++j)
                             tma_load_2d_2sm(tb, &full_bar[stage], sb + j * (BK * 128), n0 + j * 64, k0);
                     }
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == p.stages_used) { stage = 0; phase ^= 1; }
                 }
             }
         }
@@ -119,7 +119,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
                     }
                     umma_commit_2sm(&empty_bar[stage]);
                     if (kb == nk - 1) umma_commit_2sm(&tfull_bar[as]);
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == p.stages_used) { stage = 0; phase ^= 1; }
                 }
             }
         }

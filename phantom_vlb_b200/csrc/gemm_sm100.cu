@@ -52,6 +52,7 @@ struct GemmParams {
     int ldc32;
     int accum_f32;          // c_f32 += result instead of =
     int splits;             // split-K factor (fp32 accumulate outputs only): partial tiles are red.add'ed
+    int stages_used;        // pair kernel: ring depth actually used (<= G2_STAGES), tuning experiments
     int group_m;            // M-blocks swept together before moving to the next N-block (L2 residency of the A panel)
 };
 
@@ -487,6 +488,8 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream) {
     // while B streams past it. Measured sustained at M=16384: K=4096 shapes +1.5..3 % at 16, K >= 14336 shapes best at 8.
     p.group_m = a.K1 <= 8192 ? 16 : 8;
     { const char* g = getenv("VLB_GEMM_GROUP_M"); if (g && atoi(g) > 0) p.group_m = atoi(g); }
+    p.stages_used = G2_STAGES;
+    { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES) p.stages_used = atoi(g); }
     auto kern = gemm2_tcgen05_kernel<B_MN>;
     static bool attr_set = false;
     if (!attr_set) {
