@@ -129,6 +129,20 @@ int vlb_ln1_affine_fwd(const void* u_f32, const void* sw_f32, const void* ln1_w,
 int vlb_ln1_affine_bwd(const void* dpooled_f32, const void* u_f32, const void* sw_f32, void* dg1_f32, void* db1_f32,
                        int B, int H, void* stream);
 
+/* ------------------------------------------------------------------ fused head optimiser for very wide readouts
+ * (BASELINE configs[3]: P ~ 250 000 voxels). The ridge gradient dW = dpred^T hrf + 2 lambda W has rank <= n_samples, so it is
+ * never materialised: vlb_head_gradnorm adds ||dW||^2 to the clip accumulator from two n x n Gram matrices (plain
+ * vlb_gemm_bf16 calls) and an elementwise pass over [n, P]; vlb_head_adamw_fused forms dW tile by tile on the tensor cores
+ * and applies clip + AdamW (same arithmetic as vlb_adamw_step) in the epilogue. Replaces, for the ridge weight only, the
+ * reference's autograd dW + clip_grad_norm_ + torch.optim.AdamW (litmodule.py:345-379). */
+int vlb_head_gradnorm(const void* dpred, const void* pred, const void* bias, const void* gram_dpred_f32,
+                      const void* gram_hrf_f32, int ld_gram, const void* wsq_f32, void* sumsq_f32, int N, long long P,
+                      float l2_lambda, void* stream);
+int vlb_head_adamw_fused(const void* dpred, int ld_dpred, const void* hrf, int ld_hrf, int n_samples, long long P, int H,
+                         void* w_f32, void* m_f32, void* v_f32, void* w_bf16, const void* sumsq_f32, float lr,
+                         float beta1, float beta2, float eps, float weight_decay, int step, float max_norm,
+                         float grad_scale, float l2_lambda, void* stream);
+
 /* ------------------------------------------------------------------ optimiser (one flat buffer of trainables)
  * clip_grad_norm_(gradient_clip_val=1) + AdamW (decoupled weight decay on every trainable) with the cosine LR value
  * passed per step; writes the bf16 working copy consumed by the GEMMs in the same sweep. grad_scale = 1/world_size

@@ -420,6 +420,33 @@ __global__ void ln1_affine_bwd_kernel(const float* __restrict__ dpooled, const f
     dg1[h] += ag; db1[h] += ab;
 }
 
+
+// ||dW||^2 of the readout weight WITHOUT forming dW = dpred^T hrf + 2*lambda*W (rank-N structure):
+//   ||dpred^T hrf||^2 = <Gd, Gh>,  Gd = dpred dpred^T, Gh = hrf hrf^T  (N x N Gram matrices from two small GEMMs)
+//   2 <dpred^T hrf, 2 lambda W> = 4 lambda sum_{n,p} dpred[n,p] * (pred[n,p] - b[p])      (pred - b = hrf W^T)
+//   ||2 lambda W||^2 = 4 lambda^2 * wsq
+// sumsq += all three. grid-stride over the N x P elements for the cross term; block 0 adds the Gram and W terms.
+__global__ void head_gradnorm_kernel(const bf16* __restrict__ dpred, const bf16* __restrict__ pred, const bf16* __restrict__ bias,
+                                     const float* __restrict__ gd, const float* __restrict__ gh, const float* __restrict__ wsq,
+                                     float* __restrict__ sumsq, int N, int ldg, long long P, float lambda) {
+    __shared__ float red[32];
+    float s = 0.f;
+    const long long total = (long long)N * P;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long pcol = i % P;
+        s += bf2f(dpred[i]) * (bf2f(pred[i]) - bf2f(bias[pcol]));
+    }
+    s *= 4.f * lambda;
+    if (blockIdx.x == 0) {
+        float g = 0.f;
+        for (int i = threadIdx.x; i < N * N; i += blockDim.x) g += gd[(i / N) * ldg + i % N] * gh[(i / N) * ldg + i % N];
+        s += g;
+        if (threadIdx.x == 0) s += 4.f * lambda * lambda * wsq[0];
+    }
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) atomicAdd(sumsq, s);
+}
+
 }  // namespace vlb
 
 using namespace vlb;
@@ -515,4 +542,16 @@ extern "C" int vlb_ln1_affine_bwd(const void* dpooled_f32, const void* u_f32, co
     ln1_affine_bwd_kernel<<<ceil_div(H, 128), 128, 0, (cudaStream_t)stream>>>(
         (const float*)dpooled_f32, (const float*)u_f32, (const float*)sw_f32, (float*)dg1_f32, (float*)db1_f32, B, H);
     return check_launch("ln1_affine_bwd");
+}
+
+extern "C" int vlb_head_gradnorm(const void* dpred, const void* pred, const void* bias, const void* gram_dpred_f32,
+                                 const void* gram_hrf_f32, int ld_gram, const void* wsq_f32, void* sumsq_f32, int N,
+                                 long long P, float l2_lambda, void* stream) {
+    VLB_REQUIRE(N > 0 && P > 0 && ld_gram >= N, "head_gradnorm: N=%d P=%lld", N, P);
+    long long blocks = ceil_div_ll((long long)N * P, 256 * 8);
+    if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
+    head_gradnorm_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        (const bf16*)dpred, (const bf16*)pred, (const bf16*)bias, (const float*)gram_dpred_f32, (const float*)gram_hrf_f32,
+        (const float*)wsq_f32, (float*)sumsq_f32, N, ld_gram, P, l2_lambda);
+    return check_launch("head_gradnorm");
 }

@@ -28,6 +28,9 @@ class Engine:
         if lora_dropout:
             raise NotImplementedError("lora_dropout > 0 is not implemented (parity and benchmark runs use 0)")
         self.saved = None
+        # wide readouts (config 3, P ~ 250k): never materialise the rank-B ridge gradient; clip norm from Gram matrices and
+        # AdamW in the epilogue of the gradient GEMM (vlb_head_gradnorm / vlb_head_adamw_fused)
+        self.fused_head_opt = self.T.num_target_local * cfg.hidden >= (1 << 26)
         self.shard_reduce = None    # callable(tensor): in-place sum across voxel shards of the readout head (config 4)
         self.launches = 0
         self.profile = None
@@ -307,7 +310,9 @@ class Engine:
         assert y.shape == (B, P) and y.dtype == torch.float32
         _l.call("vlb_head_loss", _l.ptr(pred), _l.ptr(y), _l.ptr(dpred), _l.ptr(acc), B * P, n_total, _l.cur_stream())
         _l.call("vlb_l2_prefill", _l.ptr(T.w("ridge_w")), _l.ptr(T.g("ridge_w")), _l.ptr(acc), P * H, cfg.l2_lambda,
-                int(training), _l.cur_stream())
+                int(training and not self.fused_head_opt), _l.cur_stream())
+        if self.fused_head_opt:
+            self.buf("hd_wsq_local", (1,), torch.float32).copy_(acc[1:2])      # this shard's sum of W^2 (before the reduce)
         if self.shard_reduce is not None:
             self.shard_reduce(acc)
         _l.call("vlb_loss_finalize", _l.ptr(acc), _l.ptr(out), n_total, cfg.l2_lambda, _l.cur_stream())
@@ -319,9 +324,12 @@ class Engine:
         """ridge W/b and LN2 gradients into T.grad; returns d(loss)/d(pooled) fp32 [B, H]."""
         cfg, T, hs = self.cfg, self.T, self.head_saved
         H, P = cfg.hidden, T.num_target_local
-        self.gemm(hs["dpred"], hs["hrf"], T.g("ridge_w"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+        if not self.fused_head_opt:
+            self.gemm(hs["dpred"], hs["hrf"], T.g("ridge_w"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
         _l.call("vlb_colsum", _l.ptr(hs["dpred"]), _l.ptr(T.g("ridge_b")), B, P, _l.cur_stream())
-        dhrf = self.gemm(hs["dpred"], T.w("ridge_w"), self.buf("hd_dhrf", (B, H), torch.float32), b_mn=True, out_f32=True)
+        dhrf = self.buf("hd_dhrf", (B, H), torch.float32)
+        dhrf.zero_()            # accumulate mode lets the GEMM split the P-long contraction over all SMs (red.add)
+        self.gemm(hs["dpred"], T.w("ridge_w"), dhrf, b_mn=True, out_f32=True, accumulate=True)
         if self.shard_reduce is not None:
             self.shard_reduce(dhrf)         # each voxel shard contributes a partial d(hrf); LN grads end up replicated
         dpooled = self.buf("hd_dpooled", (B, H), torch.float32)
@@ -343,6 +351,18 @@ class Engine:
         self.launches += 1
         return dx
 
+    def _zero_grads(self):
+        """Every gradient kernel ACCUMULATES (split-K red.add GEMMs, LN atomics). With the fused wide-head optimiser the
+        ridge gradient is never written, so its (multi-GB) slice of the flat buffer is not touched at all."""
+        T = self.T
+        if not self.fused_head_opt:
+            T.grad.zero_()
+            return
+        off_w, shape_w = T.offsets["ridge_w"]
+        end_w = off_w + (math.prod(shape_w) + 7) // 8 * 8
+        T.grad[:off_w].zero_()
+        T.grad[end_w:].zero_()
+
     # ------------------------------------------------------------------ steps
     def loss_and_grads(self, batch):
         """One forward + backward of training_step (litmodule.py:259-306). Returns (loss[3] fp32 device tensor, pred).
@@ -350,7 +370,7 @@ class Engine:
         freeze_backbone=True litmodule.py:86-90) keeps no activations and stops at the head."""
         B = batch["vision"].shape[0]
         lora = self.cfg.use_lora
-        self.T.grad.zero_()      # every gradient kernel below ACCUMULATES (split-K red.add GEMMs, LN atomics)
+        self._zero_grads()
         hidden, wm = self.backbone_forward(batch, save=lora)
         y = batch["timeseries"].contiguous()
         out, pred = self.head_forward(hidden, wm, y, B, training=True)
@@ -386,7 +406,7 @@ class Engine:
         cfg, T = self.cfg, self.T
         B, H = u.shape
         if training:
-            T.grad.zero_()
+            self._zero_grads()
         pre = self.buf("hd_partial1", (B, 1, H), torch.float32)
         _l.call("vlb_ln1_affine_fwd", _l.ptr(u), _l.ptr(sw), _l.ptr(T.w("ln1_w")), _l.ptr(T.w("ln1_b")), _l.ptr(pre), B, H,
                 _l.cur_stream())
@@ -405,23 +425,67 @@ class Engine:
         T = self.T
         if allreduce is not None:
             allreduce(T.grad)
+        T.step_count += 1
+        hyper = (float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), T.step_count, float(max_norm),
+                 1.0 / world_size)
+        st = _l.cur_stream()
         T.sumsq.zero_()
-        if self.shard_reduce is None:
-            _l.call("vlb_grad_sumsq", _l.ptr(T.grad), T.numel, _l.ptr(T.sumsq), _l.cur_stream())
-        else:
+        fused = self.fused_head_opt
+        off_w, shape_w = T.offsets["ridge_w"]
+        n_w = math.prod(shape_w)
+        end_w = off_w + (n_w + 7) // 8 * 8
+        gp = T.grad.data_ptr()
+
+        def sumsq(lo, hi):                      # squared norm of the materialised gradients in [lo, hi), ridge_w skipped if fused
+            for a, b in (((lo, min(hi, off_w)), (max(lo, end_w), hi)) if fused else ((lo, hi),)):
+                if b > a:
+                    _l.call("vlb_grad_sumsq", gp + 4 * a, b - a, _l.ptr(T.sumsq), st)
+                    self.launches += 1
+
+        split = T.offsets["ln1_w"][0] if self.shard_reduce is not None else T.numel
+        sumsq(0, split)
+        if fused:                               # ||dW_ridge||^2 from Gram matrices: the 4 GB gradient is never formed
+            hs, cfg = self.head_saved, self.cfg
+            N = hs["dpred"].shape[0]
+            N8 = (N + 7) // 8 * 8               # GEMM output columns come in multiples of 8: zero-padded sample rows
+            dp, hr = hs["dpred"], hs["hrf"]
+            if N8 != N:
+                dp = self.buf("hd_dpred_pad", (N8, dp.shape[1])); hr = self.buf("hd_hrf_pad", (N8, hr.shape[1]))
+                dp.zero_(); hr.zero_()
+                dp[:N].copy_(hs["dpred"]); hr[:N].copy_(hs["hrf"])
+            gd = self.buf("hd_gram_d", (N8, N8), torch.float32); gh = self.buf("hd_gram_h", (N8, N8), torch.float32)
+            gd.zero_(); gh.zero_()
+            self.gemm(dp, dp, gd, out_f32=True, accumulate=True)
+            self.gemm(hr, hr, gh, out_f32=True, accumulate=True)
+            _l.call("vlb_head_gradnorm", _l.ptr(hs["dpred"]), _l.ptr(hs["pred"]), _l.ptr(T.w("ridge_b")), _l.ptr(gd), _l.ptr(gh),
+                    N8, _l.ptr(self.buf("hd_wsq_local", (1,), torch.float32)), _l.ptr(T.sumsq), N, T.num_target_local,
+                    cfg.l2_lambda, st)
+            self.launches += 1
+        if self.shard_reduce is not None:
             # voxel-sharded head: ridge W/b gradients are rank-private (sum their squares across ranks), the LN1/LN2
             # gradients that follow them in the flat buffer are replicated (count them once)
-            split = T.offsets["ln1_w"][0]
-            _l.call("vlb_grad_sumsq", _l.ptr(T.grad), split, _l.ptr(T.sumsq), _l.cur_stream())
             self.shard_reduce(T.sumsq)
-            _l.call("vlb_grad_sumsq", T.grad.data_ptr() + 4 * split, T.numel - split, _l.ptr(T.sumsq), _l.cur_stream())
+            sumsq(split, T.numel)
+
+        def adamw(lo, hi):
+            if hi > lo:
+                _l.call("vlb_adamw_step", T.param.data_ptr() + 4 * lo, gp + 4 * lo, T.m.data_ptr() + 4 * lo,
+                        T.v.data_ptr() + 4 * lo, T.param_bf16.data_ptr() + 2 * lo, hi - lo, _l.ptr(T.sumsq), *hyper, st)
+                self.launches += 1
+
+        if fused:
+            hs, cfg = self.head_saved, self.cfg
+            adamw(0, off_w)
+            _l.call("vlb_head_adamw_fused", _l.ptr(hs["dpred"]), hs["dpred"].stride(0), _l.ptr(hs["hrf"]), hs["hrf"].stride(0),
+                    hs["dpred"].shape[0], T.num_target_local, cfg.hidden, T.param.data_ptr() + 4 * off_w,
+                    T.m.data_ptr() + 4 * off_w, T.v.data_ptr() + 4 * off_w, T.param_bf16.data_ptr() + 2 * off_w,
+                    _l.ptr(T.sumsq), *hyper, cfg.l2_lambda, st)
             self.launches += 1
-        T.step_count += 1
-        _l.call("vlb_adamw_step", _l.ptr(T.param), _l.ptr(T.grad), _l.ptr(T.m), _l.ptr(T.v), _l.ptr(T.param_bf16), T.numel,
-                _l.ptr(T.sumsq), float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), T.step_count,
-                float(max_norm), 1.0 / world_size, _l.cur_stream())
+            adamw(end_w, T.numel)
+        else:
+            adamw(0, T.numel)
         T.stage_b()
-        self.launches += 2 + 7 * T.lora_layers
+        self.launches += 7 * T.lora_layers
 
     def train_step(self, batch, lr, **opt):
         out, _ = self.loss_and_grads(batch)

@@ -127,3 +127,29 @@ def test_voxel_sharded_head_equals_unsharded():
         assert rel(e.T.g("ridge_w"), g_full["ridge_w"][lo:hi]) < 1e-5
         for k in ("ln1_w", "ln2_w", "ln2_b"):
             assert rel(e.T.g(k), g_full[k]) < 1e-3, k
+
+
+@pytest.mark.parametrize("lr_scale", [1.0])
+def test_fused_head_optimizer_matches_materialised_gradient(lr_scale):
+    """Wide-readout path (vlb_head_gradnorm + vlb_head_adamw_fused): the clip norm from Gram matrices and the AdamW update
+    in the gradient GEMM's epilogue must reproduce the materialised-gradient path (dW GEMM + vlb_grad_sumsq +
+    vlb_adamw_step) over several steps, with and without the clip being active."""
+    _, batch, cfg, e_ref = build_frozen(4)
+    _, _, _, e_fus = build_frozen(4)
+    e_fus.fused_head_opt = True
+    assert not e_ref.fused_head_opt
+    dev = {k: v.cuda() for k, v in batch.items()}
+    u, sw = e_ref.extract_features(dev)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    for step in range(4):
+        y = dev["timeseries"] * (30.0 if step % 2 == 0 else 0.01) + torch.randn(dev["timeseries"].shape, device="cuda", generator=g)
+        for e in (e_ref, e_fus):
+            e.cached_loss_and_grads(u, sw, y)
+            e.optimizer_step(1e-3 * lr_scale)
+        torch.cuda.synchronize()
+        assert abs(float(e_ref.T.sumsq) - float(e_fus.T.sumsq)) <= 1e-4 * float(e_ref.T.sumsq), "clip norm, step %d" % step
+        for name in ("ridge_w", "ridge_b", "ln1_w", "ln2_b"):
+            a, b = e_fus.T.p(name), e_ref.T.p(name)
+            assert float((a - b).abs().max()) <= 2e-6 + 1e-5 * float(b.abs().max()), "%s step %d" % (name, step)
+        assert torch.equal(e_fus.T.w("ridge_w"), e_fus.T.p("ridge_w").bfloat16())
+    assert float(e_fus.T.g("ridge_w").abs().max()) == 0.0          # the ridge gradient was never written
