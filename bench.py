@@ -101,11 +101,12 @@ def host_batches(mc, B, n, seed):
     return res
 
 
-def lit_config(P=1000):
+def lit_config(P=1000, lora_dropout=0.0, dropout_rate=0.0):
     from phantom_vlb_b200.litmodule import VLBLitModuleConfig
-    # config/experiment/VLB_vllama2_friends_lora.yaml:19-40 (dropouts 0: throughput is unaffected, parity is exact)
+    # config/experiment/VLB_vllama2_friends_lora.yaml:19-40. Default dropouts 0 (deterministic, parity-exact); the yaml's
+    # lora_dropout 0.1 / dropout_rate 0.1 are reachable with --lora-dropout / --head-dropout (masked-adapter path).
     return VLBLitModuleConfig(model_path="random:7b", freeze_backbone=False, use_lora=True, lora_r=16, lora_alpha=32,
-                              lora_dropout=0.0, dropout_rate=0.0, num_target=P, l2_lambda=0.001, lr=1e-4,
+                              lora_dropout=lora_dropout, dropout_rate=dropout_rate, num_target=P, l2_lambda=0.001, lr=1e-4,
                               betas=[0.9, 0.999], eps=1e-8, weight_decay=1e-2, lr_scheduler_name="CosineAnnealingLR",
                               last_epoch=-1, t_max=50000)
 
@@ -124,7 +125,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B, K, Wm = args.batch, args.steps, max(args.warmup, 3)
-    cfg = lit_config()
+    cfg = lit_config(lora_dropout=args.lora_dropout, dropout_rate=args.head_dropout)
     module = VLBLitModule(cfg)
     module.configure_model(device=dev, seed=1234)            # identical weights on every rank
     eng, mc = module.engine, module.model_config
@@ -212,7 +213,7 @@ def run_ours(args):
                "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                "config": {"workload": "VideoLLaMA2-7B (CLIP ViT-L/14-336 23L + STC + Mistral-7B 32L) LoRA r=16 bf16, "
                                       "8-frame 336^2 clips, 1000-parcel head, S=2048 (BASELINE configs[%d])" % (1 if world == 1 else 2),
-                          "clips_per_gpu": B, "global_batch": B * world, "parallelism": "dp%d" % world,
+                          "clips_per_gpu": B, "global_batch": B * world, "lora_dropout": args.lora_dropout, "head_dropout": args.head_dropout, "parallelism": "dp%d" % world,
                           "weights": "random-init, frozen bf16; LoRA A kaiming / B zero; fp32 master + Adam state",
                           "l2_policy": "per-step working set (>%d GB activations) far exceeds the 126 MB L2; two alternating input batches" % (B * 9 // 4)},
                "e2e": {"value": round(e2e_value, 4), "unit": "clips/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
@@ -292,6 +293,8 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="clips per GPU per step (8 x 2048 tokens: ~95 GB of the 180 GB HBM)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lora-dropout", type=float, default=0.0, help="peft lora_dropout (reference yaml: 0.1)")
+    ap.add_argument("--head-dropout", type=float, default=0.0, help="dropout_rate of the brain head (reference yaml: 0.1)")
     args = ap.parse_args()
     res = run_reference(args) if args.impl == "reference" else run_ours(args)
     if res is not None:

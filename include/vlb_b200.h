@@ -116,6 +116,15 @@ int vlb_hrf_pool_bwd(const void* x, const void* norm_w, const void* ln1_w, const
                      const void* dpooled_f32, void* dx, void* dg1_f32, void* db1_f32, int B, int S, int H,
                      int nch, float eps_rms, float eps_ln, void* stream);
 
+/* ------------------------------------------------------------------ LoRA input dropout (peft lora.Linear: B(A(dropout(x))),
+ * reference lora_dropout 0.1, config/experiment/VLB_vllama2_friends_lora.yaml:30). Counter-based mask from (seed, element
+ * index), probability quantised to 1/256; vlb_dropout_add applies the same mask to the adapter branch of dX. mask_u8 may be
+ * NULL (test hook: 0/1 bytes [M, K] so the oracle can replay the mask). */
+int vlb_dropout(const void* x, int ldx, void* out, int ldo, void* mask_u8, long long M, int K, float p,
+                unsigned long long seed, void* stream);
+int vlb_dropout_add(const void* t, int ldt, void* y, int ldy, long long M, int K, float p, unsigned long long seed,
+                    void* stream);
+
 /* ------------------------------------------------------------------ cached pooled features (frozen-backbone baseline)
  * reference: src/preprocessing/videollama2_vlb_extractfeatures.py + VLB_vllama2_friends_baseline.yaml:26-27 recompute
  * the frozen backbone every epoch; here (u, sw) = (sum_s w_s LN1hat(x_s), sum_s w_s) is extracted once per sample

@@ -235,6 +235,56 @@ __global__ void swiglu_bwd_kernel(const bf16* __restrict__ gu, const bf16* __res
     }
 }
 
+// --------------------------------------------------------------------------------------------- LoRA input dropout
+// peft lora.Linear computes B(A(dropout(x))) (reference lora_dropout = 0.1, VLB_vllama2_friends_lora.yaml:30). The keep
+// mask is a counter-based hash of (seed, row * K + col): it is regenerated, never stored, so the backward pass applies the
+// identical mask to the adapter's input gradient. One 64-bit mix per 8 consecutive elements (one byte each).
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+// keep bit of element j (0..7) of 8-chunk `chunk`: byte j of the hash compared with round(p * 256)
+__device__ __forceinline__ unsigned long long drop_bits(unsigned long long seed, long long chunk) {
+    return mix64(seed + (unsigned long long)chunk * 0x9E3779B97F4A7C15ull);
+}
+// out = x * keep / (1 - p)   (mask_out, if given, receives 0/1 bytes: test hook so an oracle can replay the mask)
+__global__ void dropout_kernel(const bf16* __restrict__ x, int ldx, bf16* __restrict__ out, int ldo, uint8_t* __restrict__ mask_out,
+                               long long M, int K, unsigned thr, float inv_keep, unsigned long long seed) {
+    const int cpr = K / 8;
+    const long long total = M * cpr;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / cpr; const int c = (int)(i % cpr);
+        float v[8];
+        load8(x + row * ldx + c * 8, v);
+        const unsigned long long h = drop_bits(seed, i);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const bool keep = ((unsigned)(h >> (8 * j)) & 0xFFu) >= thr;
+            v[j] = keep ? v[j] * inv_keep : 0.f;
+            if (mask_out) mask_out[row * K + c * 8 + j] = keep ? 1 : 0;
+        }
+        store8(out + row * ldo + c * 8, v);
+    }
+}
+// y += t * keep / (1 - p) with the SAME mask (adapter branch of the input gradient)
+__global__ void dropout_add_kernel(const bf16* __restrict__ t, int ldt, bf16* __restrict__ y, int ldy, long long M, int K,
+                                   unsigned thr, float inv_keep, unsigned long long seed) {
+    const int cpr = K / 8;
+    const long long total = M * cpr;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / cpr; const int c = (int)(i % cpr);
+        float a[8], b[8];
+        load8(t + row * ldt + c * 8, a);
+        load8(y + row * ldy + c * 8, b);
+        const unsigned long long h = drop_bits(seed, i);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (((unsigned)(h >> (8 * j)) & 0xFFu) >= thr) b[j] += a[j] * inv_keep;
+        store8(y + row * ldy + c * 8, b);
+    }
+}
+
 static inline int ew_grid(long long total, int threads) {
     long long b = ceil_div_ll(total, threads);
     long long cap = (long long)num_sms() * 16;
@@ -306,4 +356,29 @@ extern "C" int vlb_swiglu_bwd(const void* gu, const void* dact, void* dgu, long 
     swiglu_bwd_kernel<<<ew_grid(M * (I / 8), 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)gu, (const bf16*)dact,
                                                                                   (bf16*)dgu, M, I);
     return check_launch("swiglu_bwd");
+}
+
+// p is quantised to 1/256 (0.1 -> 26/256 = 0.1016); the scale uses the quantised value so E[dropout(x)] = x exactly
+static inline void drop_params(float p, unsigned* thr, float* inv_keep) {
+    unsigned t = (unsigned)(p * 256.f + 0.5f);
+    if (t > 255) t = 255;
+    *thr = t; *inv_keep = 256.f / (float)(256 - t);
+}
+
+extern "C" int vlb_dropout(const void* x, int ldx, void* out, int ldo, void* mask_u8, long long M, int K, float p,
+                           unsigned long long seed, void* stream) {
+    VLB_REQUIRE(K % 8 == 0 && ldx % 8 == 0 && ldo % 8 == 0 && p >= 0.f && p < 1.f, "dropout: K=%d ld=%d,%d p=%g", K, ldx, ldo, p);
+    unsigned thr; float ik; drop_params(p, &thr, &ik);
+    dropout_kernel<<<ew_grid(M * (K / 8), 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, ldx, (bf16*)out, ldo,
+                                                                               (uint8_t*)mask_u8, M, K, thr, ik, seed);
+    return check_launch("dropout");
+}
+
+extern "C" int vlb_dropout_add(const void* t, int ldt, void* y, int ldy, long long M, int K, float p,
+                               unsigned long long seed, void* stream) {
+    VLB_REQUIRE(K % 8 == 0 && ldt % 8 == 0 && ldy % 8 == 0 && p >= 0.f && p < 1.f, "dropout_add: K=%d ld=%d,%d p=%g", K, ldt, ldy, p);
+    unsigned thr; float ik; drop_params(p, &thr, &ik);
+    dropout_add_kernel<<<ew_grid(M * (K / 8), 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)t, ldt, (bf16*)y, ldy, M, K,
+                                                                                   thr, ik, seed);
+    return check_launch("dropout_add");
 }

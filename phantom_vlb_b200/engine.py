@@ -25,8 +25,12 @@ class Engine:
         self.T = trainables if trainables is not None else Trainables(cfg, self.dev)
         self.scale = cfg.lora_alpha / cfg.lora_r
         self.dropout_rate = float(dropout_rate)
-        if lora_dropout:
-            raise NotImplementedError("lora_dropout > 0 is not implemented (parity and benchmark runs use 0)")
+        # peft applies dropout to the adapter's INPUT: B(A(dropout(x))). With p > 0 the adapter branch can no longer ride in
+        # the base GEMM's accumulator on the way back (its input gradient needs the mask), so that mode costs one extra
+        # rank-r GEMM + masked add per projection input; p = 0 (benchmarks, parity) keeps the fully fused path.
+        self.lora_dropout = float(lora_dropout or 0.0)
+        self.drop_step = 0
+        self.drop_masks = None      # test hook: dict filled with uint8 keep masks keyed by (layer, site)
         self.saved = None
         # wide readouts (config 3, P ~ 250k): never materialise the rank-B ridge gradient; clip norm from Gram matrices and
         # AdamW in the epilogue of the gradient GEMM (vlb_head_gradnorm / vlb_head_adamw_fused)
@@ -145,6 +149,42 @@ class Engine:
             xa3=self.buf(t + "xa3", (M, 2 * r)), gu=self.buf(t + "gu", (M, 2 * I)), act=self.buf(t + "act", (M, I)),
             xa4=self.buf(t + "xa4", (M, r)))
 
+    def _drop_seed(self, l, site):
+        return 0xD0C0FFEE + (self.drop_step << 12) + l * 4 + site
+
+    def _lora_in(self, x, l, site, training):
+        """Input of the LoRA A projection: x itself, or dropout(x) into a scratch buffer (regenerated in the backward)."""
+        if not (training and self.lora_dropout > 0):
+            return x
+        xd = self.buf("lora_xd_%d" % x.shape[1], tuple(x.shape))
+        mask = None
+        if self.drop_masks is not None:
+            mask = torch.empty(tuple(x.shape), device=x.device, dtype=torch.uint8)
+            self.drop_masks[(l, site)] = mask
+        ops.dropout(x, self.lora_dropout, self._drop_seed(l, site), out=xd, mask=mask)
+        self.launches += 1
+        return xd
+
+    def _lora_in_bwd(self, x, l, site):
+        if self.lora_dropout <= 0:
+            return x
+        xd = self.buf("lora_xd_%d" % x.shape[1], tuple(x.shape))
+        ops.dropout(x, self.lora_dropout, self._drop_seed(l, site), out=xd)
+        self.launches += 1
+        return xd
+
+    def _dx_with_lora(self, dy, w_base, t, a_lora, out, l, site):
+        """out = dy @ W (frozen) + adapter branch (t @ A): one GEMM with the fused k-block, or -- with LoRA dropout -- the
+        base GEMM, a rank-r GEMM and a masked add (the adapter's input gradient passes through the dropout mask)."""
+        if self.lora_dropout <= 0:
+            return self.gemm(dy, w_base, out, a2=t, b2=a_lora, b_mn=True)
+        self.gemm(dy, w_base, out, b_mn=True)
+        tmp = self.buf("lora_tmp_%d" % out.shape[1], tuple(out.shape))
+        self.gemm(t, a_lora, tmp, b_mn=True)
+        ops.dropout_add(tmp, out, self.lora_dropout, self._drop_seed(l, site))
+        self.launches += 1
+        return out
+
     def decoder_forward(self, x0, B, save=True):
         """x0 [B*S, H] (buffer L0_x) -> pre-final-norm hidden [B*S, H]."""
         cfg, W, T = self.cfg, self.W, self.T
@@ -159,26 +199,26 @@ class Engine:
             nxt = self.buf("L%d_x" % (l + 1), (M, cfg.hidden)) if save else self.buf("Lx_%d" % (l & 1), (M, cfg.hidden))
             ops.rmsnorm_fwd(x, L["ln1_w"], cfg.rms_eps, out=b["xn1"], rstd=b["rstd1"])
             if lora:
-                self.gemm(b["xn1"], T.w(p + "Acat_qkv"), b["xa1"], alpha=s)
+                self.gemm(self._lora_in(b["xn1"], l, 0, save), T.w(p + "Acat_qkv"), b["xa1"], alpha=s)
                 self.gemm(b["xn1"], L["wqkv"], b["qkv"], a2=b["xa1"], b2=bc["qkv"])
             else:
                 self.gemm(b["xn1"], L["wqkv"], b["qkv"])
             ops.rope_(b["qkv"], W.llm["cos"], W.llm["sin"], S, cfg.heads + cfg.kv_heads, D)
             ops.attn_fwd_into(b["qkv"], b["o"], b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True)
             if lora:
-                self.gemm(b["o"], T.w(p + "A_o"), b["xa2"], alpha=s)
+                self.gemm(self._lora_in(b["o"], l, 1, save), T.w(p + "A_o"), b["xa2"], alpha=s)
                 self.gemm(b["o"], L["wo"], b["h1"], a2=b["xa2"], b2=bc["o"], residual=x)
             else:
                 self.gemm(b["o"], L["wo"], b["h1"], residual=x)
             ops.rmsnorm_fwd(b["h1"], L["ln2_w"], cfg.rms_eps, out=b["xn2"], rstd=b["rstd2"])
             if lora:
-                self.gemm(b["xn2"], T.w(p + "Acat_gu"), b["xa3"], alpha=s)
+                self.gemm(self._lora_in(b["xn2"], l, 2, save), T.w(p + "Acat_gu"), b["xa3"], alpha=s)
                 self.gemm(b["xn2"], L["wgu"], b["gu"], a2=b["xa3"], b2=bc["gu"])
             else:
                 self.gemm(b["xn2"], L["wgu"], b["gu"])
             ops.swiglu_fwd(b["gu"], out=b["act"])
             if lora:
-                self.gemm(b["act"], T.w(p + "A_d"), b["xa4"], alpha=s)
+                self.gemm(self._lora_in(b["act"], l, 3, save), T.w(p + "A_d"), b["xa4"], alpha=s)
                 self.gemm(b["act"], L["wd"], nxt, a2=b["xa4"], b2=bc["d"], residual=b["h1"])
             else:
                 self.gemm(b["act"], L["wd"], nxt, residual=b["h1"])
@@ -212,21 +252,21 @@ class Engine:
             x = self.buf("L%d_x" % l, (M, H))
             # ---- down_proj: x_next = h1 + act Wd^T + s (act A_d^T) B_d^T
             self.gemm(dx, bc["d"], t16, b_mn=True, alpha=s)
-            self.gemm(dx, L["wd"], dact, a2=t16, b2=T.w(p + "A_d"), b_mn=True)
-            self.gemm(t16, b["act"], T.g(p + "A_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self._dx_with_lora(dx, L["wd"], t16, T.w(p + "A_d"), dact, l, 3)
+            self.gemm(t16, self._lora_in_bwd(b["act"], l, 3), T.g(p + "A_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa4"], dx, T.g(p + "Bt_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             ops.swiglu_bwd(b["gu"], dact, out=dgu)
             # ---- gate/up
             self.gemm(dgu, bc["gu"], t32, b_mn=True, alpha=s)
-            self.gemm(dgu, L["wgu"], dxn, a2=t32, b2=T.w(p + "Acat_gu"), b_mn=True)
-            self.gemm(t32, b["xn2"], T.g(p + "Acat_gu"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self._dx_with_lora(dgu, L["wgu"], t32, T.w(p + "Acat_gu"), dxn, l, 2)
+            self.gemm(t32, self._lora_in_bwd(b["xn2"], l, 2), T.g(p + "Acat_gu"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa3"][:, 0:r], dgu[:, 0:I], T.g(p + "Bt_g"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa3"][:, r:2 * r], dgu[:, I:2 * I], T.g(p + "Bt_u"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             ops.rmsnorm_bwd(dxn, b["h1"], L["ln2_w"], b["rstd2"], dres=dx, out=dh1)
             # ---- o_proj: h1 = x + o Wo^T + s (o A_o^T) B_o^T
             self.gemm(dh1, bc["o"], t16, b_mn=True, alpha=s)
-            self.gemm(dh1, L["wo"], do, a2=t16, b2=T.w(p + "A_o"), b_mn=True)
-            self.gemm(t16, b["o"], T.g(p + "A_o"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self._dx_with_lora(dh1, L["wo"], t16, T.w(p + "A_o"), do, l, 1)
+            self.gemm(t16, self._lora_in_bwd(b["o"], l, 1), T.g(p + "A_o"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa2"], dh1, T.g(p + "Bt_o"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             # ---- attention + RoPE
             ops.attn_bwd(b["qkv"], b["o"], do, b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True, dqkv=dqkv, dq_f32=dq32,
@@ -235,13 +275,13 @@ class Engine:
             ops.rope_(dqkv[:, nq:], W.llm["cos"], W.llm["sin"], S, cfg.kv_heads, D, inverse=True)
             # ---- q/k/v
             self.gemm(dqkv, bc["qkv"], t48, b_mn=True, alpha=s)
-            self.gemm(t48, b["xn1"], T.g(p + "Acat_qkv"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self.gemm(t48, self._lora_in_bwd(b["xn1"], l, 0), T.g(p + "Acat_qkv"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, 0:r], dqkv[:, 0:nq], T.g(p + "Bt_q"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.launches += 7
             if l > 0:        # the spliced embeddings are frozen: layer 0 needs no input gradient
-                self.gemm(dqkv, L["wqkv"], dxn, a2=t48, b2=T.w(p + "Acat_qkv"), b_mn=True)
+                self._dx_with_lora(dqkv, L["wqkv"], t48, T.w(p + "Acat_qkv"), dxn, l, 0)
                 nxt = dxa if dx.data_ptr() != dxa.data_ptr() else dxb
                 ops.rmsnorm_bwd(dxn, x, L["ln1_w"], b["rstd1"], dres=dh1, out=nxt)
                 self.launches += 1
@@ -370,6 +410,7 @@ class Engine:
         freeze_backbone=True litmodule.py:86-90) keeps no activations and stops at the head."""
         B = batch["vision"].shape[0]
         lora = self.cfg.use_lora
+        self.drop_step += 1          # fresh LoRA dropout masks every training step (same masks in its backward)
         self._zero_grads()
         hidden, wm = self.backbone_forward(batch, save=lora)
         y = batch["timeseries"].contiguous()

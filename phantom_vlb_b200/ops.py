@@ -265,3 +265,18 @@ def attn_fwd_into(qkv, out, lse, B, S, Hq, Hkv, D, causal, scale=None):
     _l.call("vlb_attn_fwd", base, base + Hq * D * 2, base + (Hq + Hkv) * D * 2, qkv.stride(0), _l.ptr(out),
             out.stride(0), _l.ptr(lse), B, S, Hq, Hkv, D, int(causal), float(scale), _l.cur_stream())
     return out
+
+
+def dropout(x, p, seed, out=None, mask=None):
+    """out = x * keep / (1 - p) with a counter-based mask of (seed, element index); mask (uint8 [M, K]) is a test hook."""
+    M, K = x.shape
+    out = torch.empty((M, K), device=x.device, dtype=x.dtype) if out is None else out
+    _l.call("vlb_dropout", _l.ptr(x), x.stride(0), _l.ptr(out), out.stride(0), _l.ptr(mask), M, K, float(p), int(seed), _st())
+    return out
+
+
+def dropout_add(t, y, p, seed):
+    """y += t * keep / (1 - p) with the same mask dropout(x, p, seed) used."""
+    M, K = t.shape
+    _l.call("vlb_dropout_add", _l.ptr(t), t.stride(0), _l.ptr(y), y.stride(0), M, K, float(p), int(seed), _st())
+    return y

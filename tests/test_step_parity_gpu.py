@@ -36,11 +36,15 @@ def build(cfg_ref, B, seed=1234):
     return ref, batch, cfg, eng
 
 
-def check_step(ref, batch, cfg, eng, tol_loss=1e-2, tol_pred=2e-2, tol_grad=6e-2):
-    out = ref.step(batch)
-    out["loss"].backward()
+def check_step(ref, batch, cfg, eng, tol_loss=1e-2, tol_pred=2e-2, tol_grad=6e-2, between=None):
+    """`between(ref, eng)` runs after the engine step and before the oracle step (e.g. to replay dropout masks)."""
     loss3, pred = eng.loss_and_grads(to_dev(batch))
     torch.cuda.synchronize()
+    loss3, pred = loss3.clone(), pred.clone()
+    if between is not None:
+        between(ref, eng)
+    out = ref.step(batch)
+    out["loss"].backward()
     B = batch["vision"].shape[0]
     errs = {}
     errs["weight_mask"] = float((eng.buf("hd_partial", (1,), torch.float32).new_zeros(1)).sum())  # placeholder 0
@@ -108,3 +112,44 @@ def test_train_step_parity_tiny():
     from oracle.ref_model import tiny_config
     ref, batch, cfg, eng = build(tiny_config(), 2)
     check_step(ref, batch, cfg, eng)
+
+
+def test_train_step_parity_with_lora_dropout():
+    """lora_dropout = 0.1 (the reference's LoRA experiment, VLB_vllama2_friends_lora.yaml:30): the engine's counter-based keep
+    masks are captured and replayed inside the oracle's peft-style LoRA linears (B(A(dropout(x)))), so loss, readout and
+    every LoRA / head gradient can be compared exactly as in the dropout-free test. q/k/v (and gate/up) adapters share one
+    mask of their common input in this build; peft draws them independently (documented deviation)."""
+    from oracle.ref_model import LoraLinear, tiny_config
+    ref, batch, cfg, eng = build(tiny_config(), 2)
+    eng.lora_dropout = 0.1
+    eng.drop_masks = {}
+    site_of = {"q_proj": 0, "k_proj": 0, "v_proj": 0, "o_proj": 1, "gate_proj": 2, "up_proj": 2, "down_proj": 3}
+
+    class Replay(torch.nn.Module):
+        def __init__(self, mask):
+            super().__init__()
+            self.mask = mask
+
+        def forward(self, x):
+            return x * self.mask.view(x.shape) * (256.0 / (256 - 26))      # p = 0.1 is quantised to 26/256 in the kernel
+
+    def install(ref, eng):
+        assert len(eng.drop_masks) == 4 * cfg.layers
+        for l, layer in enumerate(ref.llm.layers):
+            for name, site in site_of.items():
+                parent = layer.self_attn if site < 2 else layer.mlp
+                mod = getattr(parent, name)
+                assert isinstance(mod, LoraLinear)
+                m = eng.drop_masks[(l, site)].float().cpu()
+                frac = float(m.mean())
+                assert 0.85 < frac < 0.95, "keep fraction %g" % frac
+                mod.lora_dropout = Replay(m)
+
+    check_step(ref, batch, cfg, eng, between=install)
+    # a second step draws different masks; evaluation (save=False) applies none
+    m0 = eng.drop_masks[(0, 0)].clone()
+    eng.loss_and_grads(to_dev(batch))
+    assert not torch.equal(m0, eng.drop_masks[(0, 0)])
+    eng.drop_masks = {}
+    eng.eval_step(to_dev(batch))
+    assert eng.drop_masks == {}
