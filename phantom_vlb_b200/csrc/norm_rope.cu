@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(THREADS) rmsnorm_bwd_kernel(const bf16* __rest
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     const float rstd = rstd_in[row];
-    float g[MAXV][8], xh[MAXV][8];
+    float g[MAXV][8], xh[MAXV][8], rs[MAXV][8];
     float dot = 0.f;
     const int nchunk = H / 8;
 #pragma unroll
@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(THREADS) rmsnorm_bwd_kernel(const bf16* __rest
             float wv[8];
             load8(dy + row * H + c * 8, g[i]);
             load8(x + row * H + c * 8, xh[i]);
+            if (dres) load8(dres + row * H + c * 8, rs[i]);      // issued before the row reduction, not after it
             load8(w + c * 8, wv);
 #pragma unroll
             for (int j = 0; j < 8; ++j) { g[i][j] *= wv[j]; xh[i][j] *= rstd; dot += g[i][j] * xh[i][j]; }
@@ -79,9 +80,8 @@ __global__ void __launch_bounds__(THREADS) rmsnorm_bwd_kernel(const bf16* __rest
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
             if (dres) {
-                float r[8]; load8(dres + row * H + c * 8, r);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] += r[j];
+                for (int j = 0; j < 8; ++j) o[j] += rs[i][j];
             }
             store8(dx + row * H + c * 8, o);
         }
