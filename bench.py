@@ -272,9 +272,61 @@ def cpu_reference(steps, warmup, budget_s):
             "sample_seconds_per_step": round(t_step, 3), "steps_timed": len(times), "build_seconds": round(build_s, 1)}
 
 
+def gpu_torch_reference(B, steps, warmup):
+    """OPTIONAL context number (`--impl reference --ref-device cuda`): the oracle module itself -- Hugging Face CLIP / Mistral in
+    bf16 with sdpa attention, the restated peft-style LoRA (two extra GEMMs + add per linear), torch clip_grad_norm_ + AdamW on
+    fp32 adapter/head parameters under bf16 autocast -- stepped on THIS GPU on the same synthetic clips. It stands in for "the
+    reference PyTorch/HF path on a B200" (SURVEY 8d-i); it is not the reference-arm number the driver compares (that is the CPU
+    run) and nothing of it is on the product path."""
+    import torch
+    from oracle.ref_model import RefConfig, RefVLB, enable_training, synthetic_batch
+    torch.cuda.set_device(0)
+    torch.set_default_device("cuda")
+    torch.set_default_dtype(torch.bfloat16)
+    cfg = RefConfig(attn_impl="sdpa")
+    ref = enable_training(RefVLB(cfg, seed=1234, lora_b_std=0.0))
+    torch.set_default_dtype(torch.float32)
+    params = []
+    for _, p in ref.trainable():
+        p.data = p.data.float()                    # fp32 master adapters / head, bf16 frozen backbone (bf16-mixed)
+        params.append(p)
+    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-2)
+    torch.set_default_device("cpu")
+    batch = {k: v.cuda() for k, v in synthetic_batch(cfg, B, seed=1234).items()}
+    torch.set_default_device("cuda")              # the module's glue (mask rows, splice padding) allocates with the default device
+
+    def one():
+        opt.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = ref.step(batch)
+        out["loss"].backward()
+        torch.nn.utils.clip_grad_norm_(params, 1.0)
+        opt.step()
+        return out["loss"]
+
+    for _ in range(max(warmup, 1)):
+        one()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"impl": "reference-torch-gpu", "metric": "lora_train_clips_per_sec", "value": round(B / ms * 1e3, 4), "unit": "clips/s",
+            "n_gpus": 1, "steps": steps, "ms_per_step": round(ms, 2), "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "VideoLLaMA2-7B LoRA train step via the oracle module on the GPU: HF transformers %s CLIP/Mistral "
+                                   "bf16 + sdpa attention + unfused peft-style LoRA + torch AdamW, %d clips/step" % (
+                                       __import__("transformers").__version__, B)},
+            "last_loss": float(loss), "max_mem_GB": round(torch.cuda.max_memory_allocated() / 1e9, 1)}
+
+
 def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return None
+    if args.ref_device == "cuda":
+        return gpu_torch_reference(min(args.batch, 6), args.steps, args.warmup)      # 19 GB per clip of autograd state: 6 clips fit 180 GB
     cb = cpu_reference(steps=args.steps, warmup=min(args.warmup, 1), budget_s=180.0)
     return {"impl": "reference", "metric": "lora_train_clips_per_sec", "value": cb["value"], "unit": "clips/s",
             "n_gpus": args.gpus, "steps": cb["steps_timed"], "warmup": min(args.warmup, 1),
@@ -293,6 +345,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="clips per GPU per step (8 x 2048 tokens: ~95 GB of the 180 GB HBM)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-device", default="cpu", choices=["cpu", "cuda"], help="--impl reference only: cuda = time the oracle module on this GPU (context number)")
     ap.add_argument("--lora-dropout", type=float, default=0.0, help="peft lora_dropout (reference yaml: 0.1)")
     ap.add_argument("--head-dropout", type=float, default=0.0, help="dropout_rate of the brain head (reference yaml: 0.1)")
     args = ap.parse_args()

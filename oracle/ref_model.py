@@ -63,6 +63,7 @@ class RefConfig:
     lora_alpha: int = 32
     l2_lambda: float = 0.001
     lang_w_len: int = 64
+    attn_impl: str = "eager"      # "sdpa" only for bench.py's same-GPU timing of this module (parity runs stay eager, fp32)
 
     @property
     def grid(self):
@@ -168,14 +169,14 @@ class RefVLB(nn.Module):
         vc = CLIPVisionConfig(hidden_size=cfg.vit_hidden, intermediate_size=cfg.vit_mlp, num_hidden_layers=cfg.vit_layers,
                               num_attention_heads=cfg.vit_heads, image_size=cfg.image_size, patch_size=cfg.patch_size,
                               hidden_act="quick_gelu", layer_norm_eps=1e-5, projection_dim=cfg.vit_hidden)
-        vc._attn_implementation = "eager"
+        vc._attn_implementation = cfg.attn_impl
         self.vision_tower = CLIPVisionModel(vc)
         self.mm_projector = STCConnector(cfg)
         mc = MistralConfig(vocab_size=cfg.vocab, hidden_size=cfg.hidden, intermediate_size=cfg.mlp,
                            num_hidden_layers=cfg.layers, num_attention_heads=cfg.heads, num_key_value_heads=cfg.kv_heads,
                            head_dim=cfg.hidden // cfg.heads, rms_norm_eps=cfg.rms_eps, rope_theta=cfg.rope_theta,
                            sliding_window=None, max_position_embeddings=max(cfg.max_len, 4096), use_cache=False)
-        mc._attn_implementation = "eager"
+        mc._attn_implementation = cfg.attn_impl
         self.llm = MistralModel(mc)
         for p in self.parameters():
             p.requires_grad_(False)
