@@ -138,6 +138,21 @@ int vlb_ln1_affine_fwd(const void* u_f32, const void* sw_f32, const void* ln1_w,
 int vlb_ln1_affine_bwd(const void* dpooled_f32, const void* u_f32, const void* sw_f32, void* dg1_f32, void* db1_f32,
                        int B, int H, void* stream);
 
+/* Forward gate/up projection of the decoder MLP with SwiGLU fused into the GEMM epilogue (MistralMLP.forward:
+ * act_fn(gate_proj(x)) * up_proj(x), reached through videollama2_mistral.py:94-104): gu[M, 2I] (kept for the backward) and
+ * act[M, I] leave the kernel together; wgu is [2I, K] gate rows then up rows; A2/B2 = the fused LoRA k-block as in
+ * vlb_gemm_bf16. CTA-pair kernel: the leader stages gate rows, the peer the matching up rows. */
+int vlb_gemm_gateup_swiglu(const void* x, int ldx, const void* wgu, int ldw, void* gu, int ldgu, void* act, int ldact,
+                           int M, int I, int K, const void* A2, int lda2, const void* B2, int ldb2, int K2, float alpha,
+                           void* stream);
+
+/* Backward of the decoder MLP's down projection with the SwiGLU backward fused into the GEMM epilogue (autograd of
+ * MistralMLP.forward): d(act) = dy Wd (+ LoRA k-block A2/B2) stays in TMEM and dgu[M, 2I] = [d(act) up silu'(gate) |
+ * d(act) silu(gate)] is written directly from the saved gu[M, 2I]. wd is the forward weight [H, I]; I % 256 == 0. */
+int vlb_gemm_down_dx_swiglu_bwd(const void* dy, int lddy, const void* wd, int ldw, const void* gu, int ldgu, void* dgu,
+                                int lddgu, int M, int I, int H, const void* A2, int lda2, const void* B2, int ldb2, int K2,
+                                float alpha, void* stream);
+
 /* ------------------------------------------------------------------ fused head optimiser for very wide readouts
  * (BASELINE configs[3]: P ~ 250 000 voxels). The ridge gradient dW = dpred^T hrf + 2 lambda W has rank <= n_samples, so it is
  * never materialised: vlb_head_gradnorm adds ||dW||^2 to the clip accumulator from two n x n Gram matrices (plain

@@ -47,6 +47,10 @@ __device__ __forceinline__ void load8(const bf16* p, float (&v)[8]) {
     float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
     v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
 }
+__device__ __forceinline__ void unpack8(const uint4& u, float (&v)[8]) {
+    float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
 __device__ __forceinline__ void store8(bf16* p, const float (&v)[8]) {
     uint4 u;
     u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);

@@ -23,12 +23,19 @@ constexpr int G2_STAGES = SMEM_AB_BYTES / G2_STAGE_BYTES;    // 6
 constexpr int G2_SMEM_BYTES = G2_STAGES * G2_STAGE_BYTES + 2 * CD_STAGE_BYTES + 1024 + 256;
 constexpr int G2_TMEM_COLS = 512;
 
-template <bool B_MN>
+// SWIGLU (forward gate/up projection, B = [gate rows | up rows] of length I each): tile column block j pairs gate features
+// [128 j, +128) (leader's B half) with the SAME up features (peer's B half, rows I + 128 j), so every epilogue thread holds g
+// and u of 128 features of its row: it writes gu in the standard [M, 2I] layout (two column offsets) AND act = silu(g) * u
+// through tmAct -- the separate SwiGLU pass (read 2I, write I per token) disappears.
+// SWIGLU == 2 (backward of the down projection, N = I): the accumulator is d(act); the epilogue reads gate/up of its row
+// from gu [M, 2I] and writes dgu = [d(act) up silu'(gate) | d(act) silu(gate)] at column offsets n and I + n (I % 256 == 0),
+// so d(act) never goes to memory and the separate SwiGLU backward pass (read 3I, write 2I per token) disappears.
+template <bool B_MN, int SWIGLU = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm2_tcgen05_kernel(const GemmParams p,
                      const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                     const __grid_constant__ CUtensorMap tmC) {
+                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAct) {
     constexpr int STAGES = G2_STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -70,7 +77,8 @@ gemm2_tcgen05_kernel(const GemmParams p,
             int stage = 0; uint32_t phase = 0;
             for (int t = pair; t < num_tiles; t += num_pairs) {
                 int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb);
-                const int m0 = mb * (2 * BM) + (int)rank * BM, n0 = nb * G2_BN + (int)rank * G2_HALF_N;
+                const int m0 = mb * (2 * BM) + (int)rank * BM;
+                const int n0 = SWIGLU == 1 ? nb * G2_HALF_N + (int)rank * p.swiglu_I : nb * G2_BN + (int)rank * G2_HALF_N;
                 for (int kb = 0; kb < nk; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * G2_STAGE_BYTES);
@@ -139,6 +147,113 @@ gemm2_tcgen05_kernel(const GemmParams p,
             tc_fence_after();
             const int m = m0 + row;
             const bool m_ok = m < p.M;
+            if constexpr (SWIGLU == 2) {
+                uint8_t* cdg = smem_cd;
+                uint8_t* cdu = smem_cd + CD_STAGE_BYTES;
+                const int I = p.swiglu_I;
+                const bf16* gurow = p.sw_gu + (size_t)(m_ok ? m : 0) * p.sw_ld;
+#pragma unroll 1
+                for (int s = 0; s < G2_BN / 64; ++s) {
+                    if (issuer) tma_store_wait_read<0>();
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int c0 = s * 64 + h * 32;
+                        const int n = n0 + c0;
+                        uint4 gv[4], uv[4];
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {           // this row's gate/up values: issued before the TMEM wait
+                            gv[c] = __ldg(reinterpret_cast<const uint4*>(gurow + n + c * 8));
+                            uv[c] = __ldg(reinterpret_cast<const uint4*>(gurow + I + n + c * 8));
+                        }
+                        uint32_t r[32];
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + c0), r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            float g[8], u[8], dg[8], du[8];
+                            unpack8(gv[c], g); unpack8(uv[c], u);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const float d = bf2f(f2bf(__uint_as_float(r[c * 8 + j]) * p.alpha));   // d(act) as the unfused path stores it
+                                const float sg = 1.f / (1.f + __expf(-g[j]));
+                                const float si = g[j] * sg;
+                                du[j] = d * si;
+                                dg[j] = d * u[j] * (sg * (1.f + g[j] * (1.f - sg)));
+                            }
+                            uint4 vg, vu;
+                            vg.x = pack_bf16(dg[0], dg[1]); vg.y = pack_bf16(dg[2], dg[3]); vg.z = pack_bf16(dg[4], dg[5]); vg.w = pack_bf16(dg[6], dg[7]);
+                            vu.x = pack_bf16(du[0], du[1]); vu.y = pack_bf16(du[2], du[3]); vu.z = pack_bf16(du[4], du[5]); vu.w = pack_bf16(du[6], du[7]);
+                            const int off = row * 128 + (((h * 4 + c) ^ (row & 7)) << 4);
+                            *reinterpret_cast<uint4*>(cdg + off) = vg;
+                            *reinterpret_cast<uint4*>(cdu + off) = vu;
+                        }
+                    }
+                    if (s == G2_BN / 64 - 1) {
+                        tc_fence_before();
+                        mbar_arrive_cluster(&tempty_bar[as], 0);
+                    }
+                    fence_proxy_async_smem();
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (issuer) {
+                        tma_store_2d(&tmC, cdg, n0 + s * 64, m0);
+                        tma_store_2d(&tmC, cdu, I + n0 + s * 64, m0);
+                        tma_store_commit();
+                    }
+                }
+                continue;
+            }
+            if constexpr (SWIGLU == 1) {
+                // staging: cd0 = gate chunk, cd1 = up chunk, cd2 = act chunk (ring stage 5 is unused in this mode)
+                uint8_t* cdg = smem_cd;
+                uint8_t* cdu = smem_cd + CD_STAGE_BYTES;
+                uint8_t* cda = smem_a + (STAGES - 1) * G2_A_BYTES;
+                const int f0 = nb * G2_HALF_N;                  // first gate/up feature of this tile
+#pragma unroll 1
+                for (int s = 0; s < G2_HALF_N / 64; ++s) {
+                    if (issuer) tma_store_wait_read<0>();       // the three staging buffers have been read out
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t rg[32], ru[32];
+                        const int c0 = s * 64 + h * 32;
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + c0), rg);
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + G2_HALF_N + c0), ru);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            float g[8], u[8], a[8];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                g[j] = bf2f(f2bf(__uint_as_float(rg[c * 8 + j]) * p.alpha));
+                                u[j] = bf2f(f2bf(__uint_as_float(ru[c * 8 + j]) * p.alpha));
+                                a[j] = bf2f(f2bf(g[j] / (1.f + __expf(-g[j])))) * u[j];      // same rounding points as swiglu_fwd
+                            }
+                            uint4 vg, vu, va;
+                            vg.x = pack_bf16(g[0], g[1]); vg.y = pack_bf16(g[2], g[3]); vg.z = pack_bf16(g[4], g[5]); vg.w = pack_bf16(g[6], g[7]);
+                            vu.x = pack_bf16(u[0], u[1]); vu.y = pack_bf16(u[2], u[3]); vu.z = pack_bf16(u[4], u[5]); vu.w = pack_bf16(u[6], u[7]);
+                            va.x = pack_bf16(a[0], a[1]); va.y = pack_bf16(a[2], a[3]); va.z = pack_bf16(a[4], a[5]); va.w = pack_bf16(a[6], a[7]);
+                            const int off = row * 128 + (((h * 4 + c) ^ (row & 7)) << 4);
+                            *reinterpret_cast<uint4*>(cdg + off) = vg;
+                            *reinterpret_cast<uint4*>(cdu + off) = vu;
+                            *reinterpret_cast<uint4*>(cda + off) = va;
+                        }
+                    }
+                    if (s == G2_HALF_N / 64 - 1) {
+                        tc_fence_before();
+                        mbar_arrive_cluster(&tempty_bar[as], 0);
+                    }
+                    fence_proxy_async_smem();
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (issuer) {
+                        tma_store_2d(&tmC, cdg, f0 + s * 64, m0);
+                        tma_store_2d(&tmC, cdu, p.swiglu_I + f0 + s * 64, m0);
+                        tma_store_2d(&tmAct, cda, f0 + s * 64, m0);
+                        tma_store_commit();
+                    }
+                }
+                continue;
+            }
 #pragma unroll 1
             for (int s = 0; s < G2_BN / 64; ++s, ++cd_idx) {
                 uint8_t* cd = smem_cd + (cd_idx & 1) * CD_STAGE_BYTES;

@@ -57,6 +57,8 @@ struct GemmParams {
     // the gradient of W[n, m] (W row-major [N, ad_ld]); it is consumed in registers and never written to memory.
     float* ad_p; float* ad_m; float* ad_v; bf16* ad_pb; const float* ad_sumsq; long long ad_ld;
     float ad_lr, ad_b1, ad_b2, ad_eps, ad_wd, ad_bc1, ad_bc2, ad_max_norm, ad_gscale, ad_two_lambda;
+    int swiglu_I;           // pair kernel, SWIGLU variants: intermediate size I
+    const bf16* sw_gu; int sw_ld;   // SWIGLU == 2: saved gate/up activations [M, 2I]
     int stages_used;        // pair kernel: ring depth actually used (<= G2_STAGES), tuning experiments
     int group_m;            // M-blocks swept together before moving to the next N-block (L2 residency of the A panel)
 };
@@ -493,7 +495,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     p.ad_ld = a.ad_ld; p.ad_lr = a.ad_lr; p.ad_b1 = a.ad_b1; p.ad_b2 = a.ad_b2; p.ad_eps = a.ad_eps; p.ad_wd = a.ad_wd;
     p.ad_bc1 = a.ad_bc1; p.ad_bc2 = a.ad_bc2; p.ad_max_norm = a.ad_max_norm; p.ad_gscale = a.ad_gscale;
     p.ad_two_lambda = a.ad_two_lambda;
-    p.stages_used = 0;
+    p.stages_used = 0; p.swiglu_I = 0; p.sw_gu = nullptr; p.sw_ld = 0;
     p.group_m = 8;
     { const char* g = getenv("VLB_GEMM_GROUP_M"); if (g && atoi(g) > 0) p.group_m = atoi(g); }
     // split-K: gradient GEMMs contract over all tokens into a tiny [r, N] output; without it only mt*nt (< 148) CTAs
@@ -523,9 +525,9 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
 }
 
 // CTA-pair launch: 256 x 256 tiles, bf16 output, K-major A (the decoder / ViT / STC linears and their dX GEMMs).
-template <bool B_MN>
-static int launch_gemm2(const GemmArgs& a, cudaStream_t stream) {
-    CUtensorMap tA1, tB1, tA2, tB2, tC;
+template <bool B_MN, int SWIGLU = 0>
+static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = nullptr, int ld_act = 0) {
+    CUtensorMap tA1, tB1, tA2, tB2, tC, tAct;
     int rc;
     if ((rc = make_tmap(&tA1, a.A1, a.K1, a.M, a.lda1, BK, BM))) return rc;
     if (!B_MN) rc = make_tmap(&tB1, a.B1, a.K1, a.N, a.ldb1, BK, G2_HALF_N);
@@ -537,7 +539,9 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream) {
         else       rc = make_tmap(&tB2, a.B2, a.N, a.K2, a.ldb2, 64, BK);
         if (rc) return rc;
     } else { tA2 = tA1; tB2 = tB1; }
-    if ((rc = make_tmap(&tC, a.C, a.N, a.M, a.ldc, 64, BM))) return rc;
+    if ((rc = make_tmap(&tC, a.C, SWIGLU == 2 ? 2 * a.N : a.N, a.M, a.ldc, 64, BM))) return rc;
+    if (SWIGLU == 1) { if ((rc = make_tmap(&tAct, act, a.N / 2, a.M, ld_act, 64, BM))) return rc; }
+    else tAct = tC;
     GemmParams p;
     p.M = a.M; p.N = a.N;
     p.nk1 = ceil_div(a.K1, BK); p.nk2 = a.K2 > 0 ? ceil_div(a.K2, BK) : 0;
@@ -545,7 +549,9 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream) {
     p.bias = reinterpret_cast<const bf16*>(a.bias);
     p.residual = reinterpret_cast<const bf16*>(a.residual);
     p.ldr = a.ldr; p.act = a.act;
-    p.mt = ceil_div(a.M, 2 * BM); p.nt = ceil_div(a.N, G2_BN);
+    p.swiglu_I = SWIGLU == 1 ? a.N / 2 : SWIGLU == 2 ? a.N : 0;
+    p.sw_gu = reinterpret_cast<const bf16*>(act); p.sw_ld = ld_act;      // SWIGLU == 2: `act` carries gu
+    p.mt = ceil_div(a.M, 2 * BM); p.nt = SWIGLU == 1 ? (a.N / 2) / G2_HALF_N : ceil_div(a.N, G2_BN);
     p.c_f32 = nullptr; p.ldc32 = 0; p.accum_f32 = 0; p.splits = 1;
     p.ad_p = nullptr; p.ad_m = nullptr; p.ad_v = nullptr; p.ad_pb = nullptr; p.ad_sumsq = nullptr; p.ad_ld = 0;
     // M-blocks (256 rows) swept together before moving to the next N-block: the A panel (group x 256 x K) stays in L2
@@ -555,8 +561,9 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream) {
     // ring depth: 6 keeps the tensor pipe 95-99 % busy; for the longest contraction (K = 28672, dX of gate/up) a 4-deep ring
     // halves the DRAM over-fetch (9.3 -> 4.5 GB per launch, ncu r01c) and is ~2 % faster under the power cap
     p.stages_used = a.K1 >= 24576 ? 4 : G2_STAGES;
+    if (SWIGLU == 1) p.stages_used = G2_STAGES - 1;      // the last ring stage is the third epilogue staging buffer
     { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES) p.stages_used = atoi(g); }
-    auto kern = gemm2_tcgen05_kernel<B_MN>;
+    auto kern = gemm2_tcgen05_kernel<B_MN, SWIGLU>;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES);
@@ -567,7 +574,7 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream) {
     int cap = (a.max_ctas > 0 ? a.max_ctas : num_sms()) / 2;
     if (pairs > cap) pairs = cap;
     if (pairs < 1) pairs = 1;
-    kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC);
+    kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC, tAct);
     return check_launch("gemm2_tcgen05_kernel");
 }
 
@@ -647,6 +654,37 @@ extern "C" int vlb_head_adamw_fused(const void* dpred, int ld_dpred, const void*
     a.ad_bc1 = 1.f - powf(beta1, (float)step); a.ad_bc2 = 1.f - powf(beta2, (float)step);
     a.ad_max_norm = max_norm; a.ad_gscale = grad_scale; a.ad_two_lambda = 2.f * l2_lambda;
     return vlb::gemm_dispatch(a, 256, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// Forward gate/up projection with SwiGLU fused into the epilogue (pair kernel): gu[M, 2I] = x Wgu^T (+ LoRA k-block) and
+// act[M, I] = bf16(silu(gate)) * up in one launch. Wgu is [2I, K] (gate rows then up rows), I % 128 == 0.
+extern "C" int vlb_gemm_gateup_swiglu(const void* x, int ldx, const void* wgu, int ldw, void* gu, int ldgu, void* act, int ldact,
+                                      int M, int I, int K, const void* A2, int lda2, const void* B2, int ldb2, int K2,
+                                      float alpha, void* stream) {
+    VLB_REQUIRE(M > 0 && I > 0 && I % 128 == 0 && K > 0, "gemm_gateup_swiglu: M=%d I=%d K=%d (I must be a multiple of 128)", M, I, K);
+    vlb::GemmArgs a;
+    a.A1 = x; a.lda1 = ldx; a.K1 = K; a.B1 = wgu; a.ldb1 = ldw;
+    a.A2 = A2; a.lda2 = lda2; a.K2 = (A2 && B2) ? K2 : 0; a.B2 = B2; a.ldb2 = ldb2;
+    a.C = gu; a.ldc = ldgu; a.c_is_f32 = 0; a.accum = 0; a.M = M; a.N = 2 * I; a.alpha = alpha;
+    a.bias = nullptr; a.residual = nullptr; a.ldr = 0; a.act = 0;
+    a.a_mn = 0; a.b_mn = 0; a.max_ctas = 0; a.split_k = 1;
+    return vlb::launch_gemm2<false, 1>(a, reinterpret_cast<cudaStream_t>(stream), act, ldact);
+}
+
+// Backward of the down projection with the SwiGLU backward in the epilogue (pair kernel): d(act) = dy Wd (+ LoRA k-block)
+// stays in TMEM; dgu[M, 2I] = [d(act) up silu'(gate) | d(act) silu(gate)] is written directly. wd is [H, I] (the forward
+// weight, read MN-major), gu [M, 2I] the saved forward activations, I % 256 == 0.
+extern "C" int vlb_gemm_down_dx_swiglu_bwd(const void* dy, int lddy, const void* wd, int ldw, const void* gu, int ldgu,
+                                           void* dgu, int lddgu, int M, int I, int H, const void* A2, int lda2, const void* B2,
+                                           int ldb2, int K2, float alpha, void* stream) {
+    VLB_REQUIRE(M > 0 && I > 0 && I % 256 == 0 && H > 0 && ldgu % 8 == 0, "gemm_down_dx_swiglu_bwd: M=%d I=%d H=%d ldgu=%d", M, I, H, ldgu);
+    vlb::GemmArgs a;
+    a.A1 = dy; a.lda1 = lddy; a.K1 = H; a.B1 = wd; a.ldb1 = ldw;
+    a.A2 = A2; a.lda2 = lda2; a.K2 = (A2 && B2) ? K2 : 0; a.B2 = B2; a.ldb2 = ldb2;
+    a.C = dgu; a.ldc = lddgu; a.c_is_f32 = 0; a.accum = 0; a.M = M; a.N = I; a.alpha = alpha;
+    a.bias = nullptr; a.residual = nullptr; a.ldr = 0; a.act = 0;
+    a.a_mn = 0; a.b_mn = 1; a.max_ctas = 0; a.split_k = 1;
+    return vlb::launch_gemm2<true, 2>(a, reinterpret_cast<cudaStream_t>(stream), const_cast<void*>(gu), ldgu);
 }
 
 extern "C" void vlb_tmap_cache_clear() { vlb::tmap_cache_clear(); }

@@ -9,6 +9,8 @@ Backward : head -> decoder layers in reverse (dX through the frozen weights, ran
 """
 import math
 
+import os
+
 import torch
 
 from . import lib as _l
@@ -38,6 +40,7 @@ class Engine:
         self.shard_reduce = None    # callable(tensor): in-place sum across voxel shards of the readout head (config 4)
         self.launches = 0
         self.profile = None
+        self.fuse_swiglu = os.environ.get("VLB_FUSE_SWIGLU", "1") != "0"
         self._bufs = {}
 
     # ------------------------------------------------------------------ buffers
@@ -65,6 +68,39 @@ class Engine:
         K2 = 0 if a2 is None else (a2.shape[0] if kw.get("a_mn") else a2.shape[1])
         self.profile.append((e0, e1, 2.0 * M * N * (K + K2), (M, N, K, K2)))
         return r
+
+    def gateup(self, x, wgu, gu, act, a2, b2):
+        """Gate/up projection + SwiGLU: one pair-GEMM launch with the activation in its epilogue when the intermediate size
+        tiles by 128 (Mistral: 14336), else the GEMM followed by the row kernel."""
+        if self.fuse_swiglu and act.shape[1] % 128 == 0 and x.shape[0] >= 256:
+            self.launches += 1
+            if self.profile is None:
+                return ops.gemm_gateup_swiglu(x, wgu, gu, act, a2=a2, b2=b2)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ops.gemm_gateup_swiglu(x, wgu, gu, act, a2=a2, b2=b2)
+            e1.record()
+            K2 = 0 if a2 is None else a2.shape[1]
+            self.profile.append((e0, e1, 2.0 * gu.shape[0] * gu.shape[1] * (x.shape[1] + K2), (gu.shape[0], gu.shape[1], x.shape[1], K2)))
+            return
+        if a2 is not None:
+            self.gemm(x, wgu, gu, a2=a2, b2=b2)
+        else:
+            self.gemm(x, wgu, gu)
+        ops.swiglu_fwd(gu, out=act)
+        self.launches += 1
+
+    def down_dx_swiglu(self, dy, wd, gu, dgu, t, a_lora):
+        self.launches += 1
+        if self.profile is None:
+            return ops.gemm_down_dx_swiglu_bwd(dy, wd, gu, dgu, a2=t, b2=a_lora)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.gemm_down_dx_swiglu_bwd(dy, wd, gu, dgu, a2=t, b2=a_lora)
+        e1.record()
+        M, H = dy.shape
+        I, K2 = wd.shape[1], t.shape[1]
+        self.profile.append((e0, e1, 2.0 * M * I * (H + K2), (M, I, H, K2)))
 
     # ------------------------------------------------------------------ vision tower (frozen, forward only)
     def vit_forward(self, pixels):
@@ -213,16 +249,13 @@ class Engine:
             ops.rmsnorm_fwd(b["h1"], L["ln2_w"], cfg.rms_eps, out=b["xn2"], rstd=b["rstd2"])
             if lora:
                 self.gemm(self._lora_in(b["xn2"], l, 2, save), T.w(p + "Acat_gu"), b["xa3"], alpha=s)
-                self.gemm(b["xn2"], L["wgu"], b["gu"], a2=b["xa3"], b2=bc["gu"])
-            else:
-                self.gemm(b["xn2"], L["wgu"], b["gu"])
-            ops.swiglu_fwd(b["gu"], out=b["act"])
+            self.gateup(b["xn2"], L["wgu"], b["gu"], b["act"], b["xa3"] if lora else None, bc["gu"] if lora else None)
             if lora:
                 self.gemm(self._lora_in(b["act"], l, 3, save), T.w(p + "A_d"), b["xa4"], alpha=s)
                 self.gemm(b["act"], L["wd"], nxt, a2=b["xa4"], b2=bc["d"], residual=b["h1"])
             else:
                 self.gemm(b["act"], L["wd"], nxt, residual=b["h1"])
-            self.launches += 5
+            self.launches += 4                          # rmsnorm x2, rope, attention (gateup counts its own)
             x = nxt
         return x
 
@@ -252,10 +285,15 @@ class Engine:
             x = self.buf("L%d_x" % l, (M, H))
             # ---- down_proj: x_next = h1 + act Wd^T + s (act A_d^T) B_d^T
             self.gemm(dx, bc["d"], t16, b_mn=True, alpha=s)
-            self._dx_with_lora(dx, L["wd"], t16, T.w(p + "A_d"), dact, l, 3)
+            fused_bwd = self.fuse_swiglu and self.lora_dropout <= 0 and I % 256 == 0 and M >= 256
+            if fused_bwd:                                   # d(act) stays in TMEM; dgu leaves the GEMM epilogue
+                self.down_dx_swiglu(dx, L["wd"], b["gu"], dgu, t16, T.w(p + "A_d"))
+            else:
+                self._dx_with_lora(dx, L["wd"], t16, T.w(p + "A_d"), dact, l, 3)
             self.gemm(t16, self._lora_in_bwd(b["act"], l, 3), T.g(p + "A_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa4"], dx, T.g(p + "Bt_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
-            ops.swiglu_bwd(b["gu"], dact, out=dgu)
+            if not fused_bwd:
+                ops.swiglu_bwd(b["gu"], dact, out=dgu)
             # ---- gate/up
             self.gemm(dgu, bc["gu"], t32, b_mn=True, alpha=s)
             self._dx_with_lora(dgu, L["wgu"], t32, T.w(p + "Acat_gu"), dxn, l, 2)
@@ -279,7 +317,7 @@ class Engine:
             self.gemm(b["xa1"][:, 0:r], dqkv[:, 0:nq], T.g(p + "Bt_q"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
-            self.launches += 7
+            self.launches += 6 if fused_bwd else 7
             if l > 0:        # the spliced embeddings are frozen: layer 0 needs no input gradient
                 self._dx_with_lora(dqkv, L["wqkv"], t48, T.w(p + "Acat_qkv"), dxn, l, 0)
                 nxt = dxa if dx.data_ptr() != dxa.data_ptr() else dxb

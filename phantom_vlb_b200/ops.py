@@ -47,6 +47,43 @@ def gemm(a, b, out=None, *, a2=None, b2=None, alpha=1.0, bias=None, residual=Non
     return out
 
 
+def gemm_gateup_swiglu(x, wgu, gu, act, *, a2=None, b2=None, alpha=1.0):
+    """gu[M, 2I] = x @ wgu.T (+ a2 @ b2.T) and act[M, I] = silu(gu[:, :I]) * gu[:, I:] from one CTA-pair GEMM launch."""
+    _chk(x, torch.bfloat16), _chk(wgu, torch.bfloat16), _chk(gu, torch.bfloat16), _chk(act, torch.bfloat16)
+    M, K = x.shape
+    I = wgu.shape[0] // 2
+    assert wgu.shape == (2 * I, K) and gu.shape == (M, 2 * I) and act.shape == (M, I) and I % 128 == 0
+    K2 = 0
+    if a2 is not None:
+        _chk(a2, torch.bfloat16), _chk(b2, torch.bfloat16)
+        K2 = a2.shape[1]
+        assert b2.shape == (2 * I, K2) and a2.shape[0] == M
+    _l.call("vlb_gemm_gateup_swiglu", _l.ptr(x), x.stride(0), _l.ptr(wgu), wgu.stride(0), _l.ptr(gu), gu.stride(0),
+            _l.ptr(act), act.stride(0), M, I, K,
+            _l.ptr(a2), a2.stride(0) if a2 is not None else 0, _l.ptr(b2), b2.stride(0) if b2 is not None else 0, K2,
+            float(alpha), _l.cur_stream())
+    return gu, act
+
+
+def gemm_down_dx_swiglu_bwd(dy, wd, gu, dgu, *, a2=None, b2=None, alpha=1.0):
+    """dgu[M, 2I] = swiglu_bwd(gu, dy @ wd (+ a2 @ b2)) from one CTA-pair GEMM launch; wd is the forward weight [H, I],
+    b2 the adapter's A [r, I]."""
+    _chk(dy, torch.bfloat16), _chk(wd, torch.bfloat16), _chk(gu, torch.bfloat16), _chk(dgu, torch.bfloat16)
+    M, H = dy.shape
+    I = wd.shape[1]
+    assert wd.shape[0] == H and gu.shape == (M, 2 * I) and dgu.shape == (M, 2 * I) and I % 256 == 0
+    K2 = 0
+    if a2 is not None:
+        _chk(a2, torch.bfloat16), _chk(b2, torch.bfloat16)
+        K2 = a2.shape[1]
+        assert b2.shape == (K2, I) and a2.shape[0] == M
+    _l.call("vlb_gemm_down_dx_swiglu_bwd", _l.ptr(dy), dy.stride(0), _l.ptr(wd), wd.stride(0), _l.ptr(gu), gu.stride(0),
+            _l.ptr(dgu), dgu.stride(0), M, I, H,
+            _l.ptr(a2), a2.stride(0) if a2 is not None else 0, _l.ptr(b2), b2.stride(0) if b2 is not None else 0, K2,
+            float(alpha), _l.cur_stream())
+    return dgu
+
+
 def attn_fwd(qkv, B, S, Hq, Hkv, D, causal, scale=None, out=None, need_lse=True):
     """Flash attention over a fused projection buffer qkv [B*S, (Hq+2*Hkv)*D] -> (o [B*S, Hq*D], lse [B,Hq,S])."""
     _chk(qkv, torch.bfloat16)

@@ -137,3 +137,49 @@ def test_gemm_cta_pair_kernel(M, N, K, R, b_mn):
     out2 = ops.gemm(a, b, b_mn=b_mn)
     torch.cuda.synchronize()
     _close(out2, _ref(a, b, None, None, 1.0, None, None, 0, False, b_mn))
+
+
+@pytest.mark.parametrize("M,I,K,R", [(256, 128, 64, 0), (256, 512, 128, 16), (4096 + 72, 1792, 1024, 48), (16384, 14336 // 4, 512, 48)])
+def test_gemm_gateup_swiglu_fused(M, I, K, R):
+    from phantom_vlb_b200 import ops
+    """The pair kernel with SwiGLU in its epilogue (leader stages gate rows, peer the matching up rows) == the plain GEMM
+    followed by the row kernel, bit for bit: gu in the standard [M, 2I] layout and act [M, I]."""
+    g = torch.Generator(device="cuda").manual_seed(M + I)
+    x = (torch.randn((M, K), device="cuda", generator=g)).bfloat16()
+    w = (torch.randn((2 * I, K), device="cuda", generator=g) * K ** -0.5).bfloat16()
+    a2 = (torch.randn((M, R), device="cuda", generator=g)).bfloat16() if R else None
+    b2 = (torch.randn((2 * I, R), device="cuda", generator=g) * 0.1).bfloat16() if R else None
+    gu_ref = ops.gemm(x, w, a2=a2, b2=b2)
+    act_ref = ops.swiglu_fwd(gu_ref)
+    gu = torch.full((M, 2 * I), float("nan"), device="cuda", dtype=torch.bfloat16)
+    act = torch.full((M, I), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.gemm_gateup_swiglu(x, w, gu, act, a2=a2, b2=b2)
+    torch.cuda.synchronize()
+    ref32 = x.float() @ w.float().t() + (a2.float() @ b2.float().t() if R else 0)
+    _close(gu, ref32)
+    assert torch.equal(gu, gu_ref), "gu differs from the unfused GEMM: max %g" % float((gu.float() - gu_ref.float()).abs().max())
+    assert torch.equal(act, act_ref), "act differs: max %g" % float((act.float() - act_ref.float()).abs().max())
+
+
+@pytest.mark.parametrize("M,I,H,R", [(256, 256, 64, 0), (256, 512, 128, 16), (4096 + 72, 1792, 1024, 16), (16384, 14336 // 4, 512, 16)])
+def test_gemm_down_dx_swiglu_bwd_fused(M, I, H, R):
+    """d(act) = dy Wd (+ t A) with the SwiGLU backward in the pair kernel's epilogue == GEMM then the row kernel, bit for bit."""
+    from phantom_vlb_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(M + I + 1)
+    dy = (torch.randn((M, H), device="cuda", generator=g)).bfloat16()
+    wd = (torch.randn((H, I), device="cuda", generator=g) * H ** -0.5).bfloat16()
+    gu = (torch.randn((M, 2 * I), device="cuda", generator=g) * 2).bfloat16()
+    t = (torch.randn((M, R), device="cuda", generator=g)).bfloat16() if R else None
+    a_l = (torch.randn((R, I), device="cuda", generator=g) * 0.1).bfloat16() if R else None
+    dact = ops.gemm(dy, wd, a2=t, b2=a_l, b_mn=True)
+    ref = ops.swiglu_bwd(gu, dact)
+    dgu = torch.full((M, 2 * I), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.gemm_down_dx_swiglu_bwd(dy, wd, gu, dgu, a2=t, b2=a_l)
+    torch.cuda.synchronize()
+    assert torch.equal(dgu, ref), "dgu differs: max %g" % float((dgu.float() - ref.float()).abs().max())
+    # and against fp32 torch on the same bf16 operands (bf16 rounding of d(act) and of the result)
+    d32 = dy.float() @ wd.float() + (t.float() @ a_l.float() if R else 0)
+    gf, uf = gu[:, :I].float(), gu[:, I:].float()
+    sg = torch.sigmoid(gf)
+    ref32 = torch.cat([d32 * uf * sg * (1 + gf * (1 - sg)), d32 * gf * sg], dim=1)
+    _close(dgu, ref32, tol=2e-2)
