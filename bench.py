@@ -198,10 +198,11 @@ def run_ours(args):
     step_ms = ms / K
     roofline = {"bound": "tensor", "kernel": "gemm2_tcgen05_kernel (cta_group::2 pair tiles 256x256) / gemm_tcgen05_kernel: decoder, ViT and STC GEMMs with the fused LoRA k-block",
                 "achieved": round(achieved, 1), "peak": peak_tf, "unit": "TFLOP/s", "frac": round(achieved / peak_tf, 4),
-                "traffic": 3.80e9 if B == 8 else None,
-                "traffic_note": "DRAM read+write bytes of ONE gate/up forward launch (M=16384, N=28672, K=4096+64) from "
-                                "profiles/r01c_ncu_full_gemm2_shapes.json (ncu --set full, B=8): 2.87 GB read + 0.92 GB written "
-                                "vs 1.31 GB algorithmic 2(MK+NK+MN); the weight panel is re-read once per 16-block M group",
+                "traffic": 3.17e9 if B == 8 else None,
+                "traffic_note": "DRAM read+write bytes of ONE gate/up forward launch with SwiGLU in its epilogue (M=16384, N=28672, "
+                                "K=4096+64) from profiles/r01d_ncu_full_gemm2_swiglu.json (ncu --set full, B=8): 1.79 GB read + 1.38 GB "
+                                "written vs 1.78 GB algorithmic 2(MK+NK+MN)+2MI (gu and act are both outputs); the weight panel is "
+                                "re-read once per 16-block M group",
                 "peak_source": peak_src, "launches_timed": len(big),
                 "how": "one extra instrumented step: CUDA events around every GEMM launch on the launching stream; achieved = sum of algorithmic 2*M*N*(K+K2) over launches with M,N >= 1024 / sum of their times. The host-side event overhead leaves short idle gaps between launches, so the power-capped SM clock can sit slightly higher than inside the plain timed step",
                 "gemm_share_of_step": round(g_ms / step_ms, 4), "all_gemm_tflops": round(g_fl / (g_ms / 1e3) / 1e12, 1),

@@ -143,6 +143,16 @@ gemm2_tcgen05_kernel(const GemmParams p,
             const int m0 = mb * (2 * BM) + (int)rank * BM, n0 = nb * G2_BN;
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
+            if constexpr (SWIGLU == 2) {                    // pull this row's gate/up segments towards L2 while the MMAs run
+                if (m0 + row < p.M) {
+                    const bf16* gr = p.sw_gu + (size_t)(m0 + row) * p.sw_ld + n0;
+#pragma unroll
+                    for (int c = 0; c < G2_BN; c += 64) {
+                        asm volatile("prefetch.global.L2 [%0];" :: "l"(gr + c));
+                        asm volatile("prefetch.global.L2 [%0];" :: "l"(gr + p.swiglu_I + c));
+                    }
+                }
+            }
             mbar_wait(&tfull_bar[as], aphase);
             tc_fence_after();
             const int m = m0 + row;
