@@ -42,7 +42,10 @@ struct AttParams {
     int Hq;
 };
 
-template <int D, bool CAUSAL>
+// PT: P stays in TMEM. The softmax threads write bf16 P over the S buffer they just read (tcgen05.st) and the PV MMA takes
+// its A operand from TMEM, so P never crosses shared memory (-32 of the 128 KB of smem traffic per key block; the kernel is
+// shared-memory-bandwidth bound) and P(j) no longer has to wait for PV(j-1) to release a staging buffer.
+template <int D, bool CAUSAL, bool PT>
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO) {
@@ -61,8 +64,8 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
     uint64_t* v_empty = bars + 7;       // [2]
     uint64_t* s_full = bars + 9;        // [2] one per S buffer
     uint64_t* p_ready = bars + 11;      // [1] count 128
-    uint64_t* pv_done = bars + 12;      // [1]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
+    uint64_t* pv_done = bars + 12;      // [2] alternating, so a waiter may lag one PV behind
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nqb = gridDim.x;
@@ -79,7 +82,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
     if (warp == 1 && lane == 0) {
         mbar_init(q_full, 1);
         for (int i = 0; i < 2; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
-        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(p_ready, 128); mbar_init(pv_done, 1);
+        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(p_ready, 128); mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
@@ -142,11 +145,15 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
 #pragma unroll
                 for (int k = 0; k < ATT_BN / 16; ++k) {
                     // A = P [128 x 64] K-major; B = V tile [64 keys x D] stored key-major rows -> MN-major operand
-                    umma_bf16(tO, make_smem_desc(pa + k * 32, 0, 1024),
-                              make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
+                    if constexpr (PT)
+                        umma_bf16_ts(tO, tS + (uint32_t)(st * ATT_BN + k * 8),
+                                     make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
+                    else
+                        umma_bf16(tO, make_smem_desc(pa + k * 32, 0, 1024),
+                                  make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
                 }
                 umma_commit(&v_empty[st]);
-                umma_commit(pv_done);
+                umma_commit(&pv_done[j & 1]);
                 if (j + 2 < nblk) issue_qk(j + 2);
             }
         }
@@ -164,24 +171,35 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN), r0);
             tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN) + 32, r1);
             tmem_ld_wait();
+            // raw scores: the softmax scale is folded into the exponent's FMA (max commutes with the positive scale)
             float s[64];
 #pragma unroll
-            for (int c = 0; c < 32; ++c) { s[c] = __uint_as_float(r0[c]) * p.scale_log2; s[32 + c] = __uint_as_float(r1[c]) * p.scale_log2; }
+            for (int c = 0; c < 32; ++c) { s[c] = __uint_as_float(r0[c]); s[32 + c] = __uint_as_float(r1[c]); }
             const int k0 = j * ATT_BN;
             const bool need_mask = (CAUSAL && k0 + ATT_BN - 1 > q0) || (k0 + ATT_BN > p.kv_len);
-            if (need_mask) {
-                const int lim = CAUSAL ? min(qrow, p.kv_len - 1) : (p.kv_len - 1);
+            if (need_mask) {                                  // block-uniform: a real branch, diagonal / ragged blocks only
+                asm volatile("" ::: "memory");
+                const int nvalid = (CAUSAL ? min(qrow, p.kv_len - 1) : (p.kv_len - 1)) - k0 + 1;
 #pragma unroll
-                for (int c = 0; c < 64; ++c) if (k0 + c > lim) s[c] = -INFINITY;
+                for (int c = 0; c < 64; ++c) s[c] = c < nvalid ? s[c] : -INFINITY;
             }
-            float mx = s[0];
+            float mx0 = fmaxf(s[0], s[1]), mx1 = fmaxf(s[2], s[3]);
 #pragma unroll
-            for (int c = 1; c < 64; ++c) mx = fmaxf(mx, s[c]);
-            if (j > 0) mbar_wait(pv_done, (j - 1) & 1);      // P buffer free again, O accumulator stable
+            for (int c = 4; c < 64; c += 4) { mx0 = fmaxf(mx0, fmaxf(s[c], s[c + 1])); mx1 = fmaxf(mx1, fmaxf(s[c + 2], s[c + 3])); }
+            const float mx = fmaxf(mx0, mx1) * p.scale_log2;
             const bool grow = mx > m_used + 8.f;
+            const bool any_grow = j > 0 && __any_sync(0xffffffffu, grow);
+            if constexpr (PT) {
+                // P(j) goes to its own S buffer: only a rescale of O needs PV(j-1) retired. PV(j-2) is consumed every
+                // iteration so the parity of each of the two alternating barriers never runs two phases ahead.
+                if (j > 1) mbar_wait(&pv_done[j & 1], ((j - 2) >> 1) & 1);
+                if (any_grow) mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+            } else {
+                if (j > 0) mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);      // P buffer free again, O accumulator stable
+            }
             if (j == 0) {
                 m_used = (mx == -INFINITY) ? 0.f : mx;
-            } else if (__any_sync(0xffffffffu, grow)) {
+            } else if (any_grow) {
                 tc_fence_after();
                 const float m_new = grow ? mx : m_used;
                 const float f = exp2f(m_used - m_new);
@@ -199,25 +217,31 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 m_used = m_new;
             }
             float sum = 0.f;
+            const float neg_m = -m_used;
+            uint32_t pk[32];                                  // PT: the row's 64 probabilities as bf16 pairs
 #pragma unroll
             for (int c8 = 0; c8 < 8; ++c8) {
                 float e[8];
 #pragma unroll
-                for (int t = 0; t < 8; ++t) { e[t] = exp2f(s[c8 * 8 + t] - m_used); }
+                for (int t = 0; t < 8; ++t) { e[t] = exp2f(fmaf(s[c8 * 8 + t], p.scale_log2, neg_m)); }
                 uint4 u;
                 u.x = pack_bf16(e[0], e[1]); u.y = pack_bf16(e[2], e[3]); u.z = pack_bf16(e[4], e[5]); u.w = pack_bf16(e[6], e[7]);
-                // accumulate the row sum from the bf16-rounded probabilities actually fed to the PV MMA
-                float2 a0 = unpack_bf16(u.x), a1 = unpack_bf16(u.y), a2 = unpack_bf16(u.z), a3 = unpack_bf16(u.w);
-                sum += (a0.x + a0.y) + (a1.x + a1.y) + (a2.x + a2.y) + (a3.x + a3.y);
-                *reinterpret_cast<uint4*>(sP + row * 128 + ((c8 ^ (row & 7)) << 4)) = u;
+                sum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));      // fp32 row sum (as flash-attn)
+                if constexpr (PT) { pk[c8 * 4] = u.x; pk[c8 * 4 + 1] = u.y; pk[c8 * 4 + 2] = u.z; pk[c8 * 4 + 3] = u.w; }
+                else *reinterpret_cast<uint4*>(sP + row * 128 + ((c8 ^ (row & 7)) << 4)) = u;
             }
             l += sum;
-            fence_proxy_async_smem();
+            if constexpr (PT) {
+                tmem_st32(tS + (uint32_t)((j & 1) * ATT_BN), pk);
+                tmem_st_wait();
+            } else {
+                fence_proxy_async_smem();
+            }
             tc_fence_before();
             mbar_arrive(p_ready);
         }
         // ---- epilogue: O / l -> bf16 -> smem (Q region, free: every QK MMA has retired) -> TMA store
-        mbar_wait(pv_done, (nblk - 1) & 1);
+        mbar_wait(&pv_done[(nblk - 1) & 1], ((nblk - 1) >> 1) & 1);
         tc_fence_after();
         const float inv_l = l > 0.f ? 1.f / l : 0.f;
 #pragma unroll 1
@@ -263,8 +287,8 @@ static int att_tmap(CUtensorMap* m, const void* ptr, int cols, int S, int B, int
     return encode_tmap_bf16(m, ptr, 3, dims, strides, box);
 }
 
-template <int D, bool CAUSAL>
-static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, float* lse, int B,
+template <int D, bool CAUSAL, bool PT>
+static int launch_attn_fwd_impl(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, float* lse, int B,
                            int S, int Hq, int Hkv, float scale, cudaStream_t st) {
     using Cfg = AttCfg<D>;
     CUtensorMap tq, tk, tv, to;
@@ -275,7 +299,7 @@ static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_q
     if ((rc = att_tmap(&to, o, Hq * D, S, B, ld_o, ATT_BM))) return rc;
     AttParams p;
     p.S = S; p.kv_len = S; p.group = Hq / Hkv; p.scale_log2 = scale * 1.4426950408889634f; p.lse = lse; p.Hq = Hq;
-    auto kern = attn_fwd_kernel<D, CAUSAL>;
+    auto kern = attn_fwd_kernel<D, CAUSAL, PT>;
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -285,6 +309,14 @@ static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_q
     dim3 grid(ceil_div(S, ATT_BM), Hq, B);
     kern<<<grid, ATT_THREADS, Cfg::SMEM_BYTES, st>>>(p, tq, tk, tv, to);
     return check_launch("attn_fwd_kernel");
+}
+
+template <int D, bool CAUSAL>
+static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, float* lse, int B,
+                           int S, int Hq, int Hkv, float scale, cudaStream_t st) {
+    static const bool pt = [] { const char* e = getenv("VLB_ATT_P_TMEM"); return !(e && e[0] == '0'); }();
+    return pt ? launch_attn_fwd_impl<D, CAUSAL, true>(q, k, v, ld_qkv, o, ld_o, lse, B, S, Hq, Hkv, scale, st)
+              : launch_attn_fwd_impl<D, CAUSAL, false>(q, k, v, ld_qkv, o, ld_o, lse, B, S, Hq, Hkv, scale, st);
 }
 
 }  // namespace vlb
