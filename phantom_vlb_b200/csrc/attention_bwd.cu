@@ -176,6 +176,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 }
                 umma_commit(dp_full);
             };
+            const bool pt = !(p.dbg & 4);
             mbar_wait(kv_full, 0);
             issue_s(0);
             issue_dp(0);
@@ -184,15 +185,29 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 const int st = t % BW_NST;
                 const uint32_t qa = smem_u32(sQ + st * Cfg::QDO_BYTES), doa = smem_u32(sDO + st * Cfg::QDO_BYTES);
                 const uint32_t pa = smem_u32(sP + (t & 1) * Cfg::PS_BYTES), dsa = smem_u32(sDS + (t & 1) * Cfg::PS_BYTES);
-                mbar_wait(pds_ready, t & 1);       // P/dS(t) in smem; S(t), dP(t) TMEM columns drained
+                mbar_wait(pds_ready, t & 1);       // P/dS(t) in smem / TMEM; S(t), dP(t) TMEM columns drained
                 tc_fence_after();
                 if (t + 1 < T) issue_dp(t + 1);
+                if (pt) {
+                    // (3)(4) with the A operand from TMEM: P^T / dS^T were packed (bf16 pairs along the query axis) over the
+                    // S buffer by the softmax threads -- warpgroup g: P^T at columns 32g..32g+15, dS^T at 32g+16..32g+31
+                    const uint32_t ta = tmem_base + Cfg::T_S + (t & 1) * BW_BQ;
 #pragma unroll
-                for (int k = 0; k < BW_BQ / 16; ++k) {          // (3) dV += P^T dO ; (4) dK += dS^T Q
-                    umma_bf16(tmem_base + Cfg::T_DV, make_smem_desc(pa + k * 32, 0, 1024),
-                              make_smem_desc(doa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
-                    umma_bf16(tmem_base + Cfg::T_DK, make_smem_desc(dsa + k * 32, 0, 1024),
-                              make_smem_desc(qa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < BW_BQ / 16; ++k) {
+                        const uint32_t ca = (uint32_t)((k >> 1) * 32 + (k & 1) * 8);
+                        umma_bf16_ts(tmem_base + Cfg::T_DV, ta + ca,
+                                     make_smem_desc(doa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
+                        umma_bf16_ts(tmem_base + Cfg::T_DK, ta + ca + 16,
+                                     make_smem_desc(qa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < BW_BQ / 16; ++k) {          // (3) dV += P^T dO ; (4) dK += dS^T Q
+                        umma_bf16(tmem_base + Cfg::T_DV, make_smem_desc(pa + k * 32, 0, 1024),
+                                  make_smem_desc(doa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
+                        umma_bf16(tmem_base + Cfg::T_DK, make_smem_desc(dsa + k * 32, 0, 1024),
+                                  make_smem_desc(qa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
+                    }
                 }
                 if (t > 0) { mbar_wait(dq_free, (t - 1) & 1); tc_fence_after(); }
 #pragma unroll
@@ -212,6 +227,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
         const uint32_t tb = tmem_base + ((uint32_t)(qd * 32) << 16);
         const int key = k0 + row;
         const int cb = wg * 32;
+        const bool pt = !(p.dbg & 4);
         auto drain_dq = [&](int t) {
             const int h = hk * p.group + t / per_head;
             const int q0 = (i_start + t % per_head) * BW_BQ;
@@ -244,17 +260,32 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 tmem_ld32(tb + Cfg::T_S + (t & 1) * BW_BQ + cb, rs);
                 tmem_ld_wait();
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    float pe = (p.dbg & 2) ? __uint_as_float(rs[c]) : exp2f(__uint_as_float(rs[c]) * p.scale_log2 - lse[c]);
-                    if (diag && key > q0 + cb + c) pe = 0.f;
-                    pv[c] = pe;
+                for (int c4 = 0; c4 < 8; ++c4) {
+                    const float4 l4 = *reinterpret_cast<const float4*>(lse + c4 * 4);
+                    pv[c4 * 4 + 0] = exp2f(fmaf(__uint_as_float(rs[c4 * 4 + 0]), p.scale_log2, -l4.x));
+                    pv[c4 * 4 + 1] = exp2f(fmaf(__uint_as_float(rs[c4 * 4 + 1]), p.scale_log2, -l4.y));
+                    pv[c4 * 4 + 2] = exp2f(fmaf(__uint_as_float(rs[c4 * 4 + 2]), p.scale_log2, -l4.z));
+                    pv[c4 * 4 + 3] = exp2f(fmaf(__uint_as_float(rs[c4 * 4 + 3]), p.scale_log2, -l4.w));
                 }
+                if (diag) {                                  // CTA-uniform: a real branch, diagonal tiles only
+                    asm volatile("" ::: "memory");
+                    const int nz = key - (q0 + cb);          // query columns c < nz lie above the diagonal (key > query)
 #pragma unroll
-                for (int c8 = 0; c8 < 4; ++c8) {
-                    uint4 u;
-                    u.x = pack_bf16(pv[c8 * 8 + 0], pv[c8 * 8 + 1]); u.y = pack_bf16(pv[c8 * 8 + 2], pv[c8 * 8 + 3]);
-                    u.z = pack_bf16(pv[c8 * 8 + 4], pv[c8 * 8 + 5]); u.w = pack_bf16(pv[c8 * 8 + 6], pv[c8 * 8 + 7]);
-                    *reinterpret_cast<uint4*>(pP + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;
+                    for (int c = 0; c < 32; ++c) pv[c] = c < nz ? 0.f : pv[c];
+                }
+                if (pt) {
+                    uint32_t pp[16];
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) pp[c] = pack_bf16(pv[2 * c], pv[2 * c + 1]);
+                    tmem_st16(tb + Cfg::T_S + (t & 1) * BW_BQ + cb, pp);      // over this thread's own (already read) S columns
+                } else {
+#pragma unroll
+                    for (int c8 = 0; c8 < 4; ++c8) {
+                        uint4 u;
+                        u.x = pack_bf16(pv[c8 * 8 + 0], pv[c8 * 8 + 1]); u.y = pack_bf16(pv[c8 * 8 + 2], pv[c8 * 8 + 3]);
+                        u.z = pack_bf16(pv[c8 * 8 + 4], pv[c8 * 8 + 5]); u.w = pack_bf16(pv[c8 * 8 + 6], pv[c8 * 8 + 7]);
+                        *reinterpret_cast<uint4*>(pP + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;
+                    }
                 }
             }
             {   // phase B: dS^T = P^T o (dP^T - Delta)
@@ -263,14 +294,22 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 tc_fence_after();
                 tmem_ld32(tb + Cfg::T_DP + cb, rp);
                 tmem_ld_wait();
+                uint32_t pd[16];
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
                     float d[8];
+                    const float4 d0 = *reinterpret_cast<const float4*>(dl + c8 * 8), d1 = *reinterpret_cast<const float4*>(dl + c8 * 8 + 4);
+                    const float dlv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) d[e] = pv[c8 * 8 + e] * (__uint_as_float(rp[c8 * 8 + e]) - dl[c8 * 8 + e]);
+                    for (int e = 0; e < 8; ++e) d[e] = pv[c8 * 8 + e] * (__uint_as_float(rp[c8 * 8 + e]) - dlv[e]);
                     uint4 u;
                     u.x = pack_bf16(d[0], d[1]); u.y = pack_bf16(d[2], d[3]); u.z = pack_bf16(d[4], d[5]); u.w = pack_bf16(d[6], d[7]);
-                    *reinterpret_cast<uint4*>(pDS + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;
+                    *reinterpret_cast<uint4*>(pDS + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;      // B operand of dQ^T
+                    pd[c8 * 4] = u.x; pd[c8 * 4 + 1] = u.y; pd[c8 * 4 + 2] = u.z; pd[c8 * 4 + 3] = u.w;
+                }
+                if (pt) {
+                    tmem_st16(tb + Cfg::T_S + (t & 1) * BW_BQ + cb + 16, pd);   // A operand of dK
+                    tmem_st_wait();
                 }
             }
             fence_proxy_async_smem();
