@@ -46,7 +46,8 @@ int vlb_gemm_bf16(const void* A, int lda, const void* B, int ldb, void* C, int l
 int vlb_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, void* lse_f32,
                  int B, int S, int Hq, int Hkv, int D, int causal, float scale, void* stream);
 
-/* Backward (head_dim 128, S % 128 == 0). delta_f32 [B,Hq,S] and dq_f32 [B*S, Hq*D] are caller-provided scratch/outputs;
+/* Backward (head_dim 128, S % 128 == 0). delta_f32 [B,Hq,S] and dq_f32 [B*S, Hq*D] are caller-provided scratch/outputs
+ * (delta_f32 is left holding scale * rowsum(dO o O): the softmax scale travels inside dS);
  * dq is accumulated in fp32 (zeroed inside) and converted by vlb_rope_bwd_f32; dk/dv are bf16 rows with stride ld_dkv. */
 int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_qkv, const void* o, const void* d_o,
                  int ld_o, const void* lse_f32, void* delta_f32, void* dq_f32, void* dk, void* dv, int ld_dkv,

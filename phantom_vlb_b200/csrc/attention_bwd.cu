@@ -129,9 +129,11 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 tma_load_3d(&tmV, kv_full, sV + c * (BW_BK * 128), hk * BW_D + c * 64, k0, b);
             }
             int st = 0; uint32_t ph = 0;
+            int hh = 0, qi = 0;                             // step t = (head hh of the group, query block qi): no division per step
             for (int t = 0; t < T; ++t) {
-                const int h = hk * p.group + t / per_head;
-                const int q0 = (i_start + t % per_head) * BW_BQ;
+                const int h = hk * p.group + hh;
+                const int q0 = (i_start + qi) * BW_BQ;
+                if (++qi == per_head) { qi = 0; ++hh; }
                 mbar_wait(&qdo_empty[st], ph ^ 1);
                 mbar_expect_tx(&qdo_full[st], 2 * Cfg::QDO_BYTES + 2 * BW_BQ * 4);
 #pragma unroll
@@ -228,9 +230,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
         const int key = k0 + row;
         const int cb = wg * 32;
         const bool pt = !(p.dbg & 4);
-        auto drain_dq = [&](int t) {
-            const int h = hk * p.group + t / per_head;
-            const int q0 = (i_start + t % per_head) * BW_BQ;
+        auto drain_dq = [&](int h, int q0) {
             float* dst = p.dq + ((size_t)b * p.S + q0 + cb) * ((size_t)p.Hq * BW_D) + (size_t)h * BW_D + row;
             uint32_t r[32];
             tmem_ld32(tb + Cfg::T_DQ + cb, r);
@@ -238,15 +238,20 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
             tc_fence_before();
             mbar_arrive(dq_free);                        // registers hold the tile: the next dQ^T MMA may overwrite TMEM
             if (!(p.dbg & 1)) {
+                if (p.Hq == 32) {                            // Mistral-7B: constant row stride -> immediate address offsets
 #pragma unroll
-                for (int c = 0; c < 32; ++c)
-                    atomicAdd(dst + (size_t)c * ((size_t)p.Hq * BW_D), __uint_as_float(r[c]) * p.scale);
+                    for (int c = 0; c < 32; ++c) atomicAdd(dst + c * (32 * BW_D), __uint_as_float(r[c]));
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) atomicAdd(dst + (size_t)c * ((size_t)p.Hq * BW_D), __uint_as_float(r[c]));
+                }
             }
         };
+        int hh = 0, qi = 0, st = 0, prev_h = 0, prev_q0 = 0;
+        uint32_t st_ph = 0;
         for (int t = 0; t < T; ++t) {
-            const int st = t % BW_NST;
-            const int q0 = (i_start + t % per_head) * BW_BQ;
-            mbar_wait(&qdo_full[st], (t / BW_NST) & 1);  // lse/delta vectors landed (bulk copies on the same barrier)
+            const int q0 = (i_start + qi) * BW_BQ;
+            mbar_wait(&qdo_full[st], st_ph);             // lse/delta vectors landed (bulk copies on the same barrier)
             const float* lse = sVec + st * 2 * BW_BQ + cb;
             const float* dl = lse + BW_BQ;
             const bool diag = p.causal && (q0 < k0 + BW_BK);      // some (key > query) pairs in this tile
@@ -301,7 +306,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                     const float4 d0 = *reinterpret_cast<const float4*>(dl + c8 * 8), d1 = *reinterpret_cast<const float4*>(dl + c8 * 8 + 4);
                     const float dlv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) d[e] = pv[c8 * 8 + e] * (__uint_as_float(rp[c8 * 8 + e]) - dlv[e]);
+                    for (int e = 0; e < 8; ++e) d[e] = pv[c8 * 8 + e] * fmaf(__uint_as_float(rp[c8 * 8 + e]), p.scale, -dlv[e]);   // scale * dS
                     uint4 u;
                     u.x = pack_bf16(d[0], d[1]); u.y = pack_bf16(d[2], d[3]); u.z = pack_bf16(d[4], d[5]); u.w = pack_bf16(d[6], d[7]);
                     *reinterpret_cast<uint4*>(pDS + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;      // B operand of dQ^T
@@ -318,13 +323,16 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
             if (t > 0) {
                 mbar_wait(mma_done, (t - 1) & 1);        // dQ^T(t-1) complete; P/dS buffer (t-1)&1 free for step t+1
                 tc_fence_after();
-                drain_dq(t - 1);
+                drain_dq(prev_h, prev_q0);
             }
+            prev_h = hk * p.group + hh; prev_q0 = q0;
+            if (++qi == per_head) { qi = 0; ++hh; }
+            if (++st == BW_NST) { st = 0; st_ph ^= 1; }
         }
         mbar_wait(mma_done, (T - 1) & 1);
         tc_fence_after();
-        drain_dq(T - 1);
-        // ---- epilogue: dV_j, dK_j (x softmax scale) -> bf16 -> global rows [b*S + key], head hk; each warpgroup 64 columns
+        drain_dq(prev_h, prev_q0);
+        // ---- epilogue: dV_j, dK_j (the softmax scale is already inside dS^T) -> bf16 -> global rows [b*S + key], head hk; each warpgroup 64 columns
         bf16* dvr = p.dv + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
         bf16* dkr = p.dk + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
 #pragma unroll 1
@@ -346,10 +354,10 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
 #pragma unroll
             for (int c8 = 0; c8 < 4; ++c8) {
                 uint4 u;
-                u.x = pack_bf16(__uint_as_float(r[c8 * 8 + 0]) * p.scale, __uint_as_float(r[c8 * 8 + 1]) * p.scale);
-                u.y = pack_bf16(__uint_as_float(r[c8 * 8 + 2]) * p.scale, __uint_as_float(r[c8 * 8 + 3]) * p.scale);
-                u.z = pack_bf16(__uint_as_float(r[c8 * 8 + 4]) * p.scale, __uint_as_float(r[c8 * 8 + 5]) * p.scale);
-                u.w = pack_bf16(__uint_as_float(r[c8 * 8 + 6]) * p.scale, __uint_as_float(r[c8 * 8 + 7]) * p.scale);
+                u.x = pack_bf16(__uint_as_float(r[c8 * 8 + 0]), __uint_as_float(r[c8 * 8 + 1]));
+                u.y = pack_bf16(__uint_as_float(r[c8 * 8 + 2]), __uint_as_float(r[c8 * 8 + 3]));
+                u.z = pack_bf16(__uint_as_float(r[c8 * 8 + 4]), __uint_as_float(r[c8 * 8 + 5]));
+                u.w = pack_bf16(__uint_as_float(r[c8 * 8 + 6]), __uint_as_float(r[c8 * 8 + 7]));
                 *reinterpret_cast<uint4*>(dkr + c0 + c8 * 8) = u;
             }
         }
@@ -362,7 +370,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
 
 // Delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]; one warp per (row, head), D = 128 -> 4 elements per lane
 __global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dO, int ld, float* __restrict__ delta,
-                                  long long rows, int S, int Hq) {
+                                  long long rows, int S, int Hq, float scale) {
     const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (w >= rows * Hq) return;
@@ -372,7 +380,7 @@ __global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __rest
     const float2 a0 = unpack_bf16(a.x), a1 = unpack_bf16(a.y), g0 = unpack_bf16(g.x), g1 = unpack_bf16(g.y);
     float s = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y;
     s = warp_sum(s);
-    if (lane == 0) delta[((size_t)(r / S) * Hq + h) * S + (r % S)] = s;
+    if (lane == 0) delta[((size_t)(r / S) * Hq + h) * S + (r % S)] = s * scale;      // pre-scaled: dS^T leaves phase B as scale * dS^T
 }
 
 static int bw_tmap(CUtensorMap* m, const void* ptr, int cols, int S, int B, int ld, int box_rows) {
@@ -397,7 +405,7 @@ extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_
     {
         const long long threads = rows * Hq * 32;
         attn_delta_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>((const bf16*)o, (const bf16*)d_o, ld_o,
-                                                                             (float*)delta_f32, rows, S, Hq);
+                                                                             (float*)delta_f32, rows, S, Hq, scale);
         int rc = check_launch("attn_delta_kernel");
         if (rc) return rc;
     }
