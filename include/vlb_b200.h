@@ -46,6 +46,10 @@ int vlb_gemm_bf16(const void* A, int lda, const void* B, int ldb, void* C, int l
 int vlb_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, void* lse_f32,
                  int B, int S, int Hq, int Hkv, int D, int causal, float scale, void* stream);
 
+/* Debug only (VLB_ATT_TS=1): clock64 stamps of the softmax / MMA-issuer hand-offs of the heaviest forward CTA, 8 per key
+ * block (tools/attn_timeline.py). */
+int vlb_attn_debug_ts(long long* host_out, int n);
+
 /* Backward (head_dim 128, S % 128 == 0). delta_f32 [B,Hq,S] and dq_f32 [B*S, Hq*D] are caller-provided scratch/outputs
  * (delta_f32 is left holding scale * rowsum(dO o O): the softmax scale travels inside dS);
  * dq is accumulated in fp32 (zeroed inside) and converted by vlb_rope_bwd_f32; dk/dv are bf16 rows with stride ld_dkv. */

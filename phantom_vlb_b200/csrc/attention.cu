@@ -24,11 +24,11 @@ template <int D> struct AttCfg {
     static constexpr int Q_BYTES = ATT_BM * D * 2;
     static constexpr int KV_BYTES = ATT_BN * D * 2;
     static constexpr int P_BYTES = ATT_BM * ATT_BN * 2;
+    static constexpr int K_STAGES = 3;                         // K is needed two key blocks ahead of V (S is issued two ahead)
     static constexpr int OFF_K = Q_BYTES;
-    static constexpr int OFF_V = OFF_K + 2 * KV_BYTES;
-    static constexpr int OFF_P = OFF_V + 2 * KV_BYTES;
-    static constexpr int OFF_BAR = OFF_P + P_BYTES;
-    static constexpr int SMEM_BYTES = OFF_BAR + 128;          // + barriers; two CTAs fit one SM
+    static constexpr int OFF_V = OFF_K + K_STAGES * KV_BYTES;
+    static constexpr int OFF_BAR = OFF_V + 2 * KV_BYTES;      // P lives in TMEM: no staging buffer
+    static constexpr int SMEM_BYTES = OFF_BAR + 256;          // + barriers; two CTAs fit one SM
     static constexpr int TMEM_COLS = 256;                     // two S buffers (64 columns each) + O (D columns); x2 CTAs = 512
     static constexpr int O_COL = 2 * ATT_BN;                  // S0 at column 0, S1 at 64, O after them
 };
@@ -40,12 +40,14 @@ struct AttParams {
     float scale_log2;   // softmax scale * log2(e)
     float* lse;         // [B, Hq, S] log2-domain logsumexp
     int Hq;
+    long long* ts;      // debug (VLB_ATT_TS=1): clock64 stamps of the hand-offs of one heavy CTA, 8 per key block
 };
 
-// PT: P stays in TMEM. The softmax threads write bf16 P over the S buffer they just read (tcgen05.st) and the PV MMA takes
+// P stays in TMEM. The softmax threads write bf16 P over the S buffer they just read (tcgen05.st) and the PV MMA takes
 // its A operand from TMEM, so P never crosses shared memory (-32 of the 128 KB of smem traffic per key block; the kernel is
 // shared-memory-bandwidth bound) and P(j) no longer has to wait for PV(j-1) to release a staging buffer.
-template <int D, bool CAUSAL, bool PT>
+#define ATT_TS(slot) do { if (ts_on) p.ts[j * 8 + (slot)] = clock64(); } while (0)
+template <int D, bool CAUSAL>
 __global__ void __launch_bounds__(ATT_THREADS, 2)
 attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO) {
@@ -55,17 +57,16 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
     uint8_t* sQ = smem;
     uint8_t* sK = smem + Cfg::OFF_K;
     uint8_t* sV = smem + Cfg::OFF_V;
-    uint8_t* sP = smem + Cfg::OFF_P;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
     uint64_t* q_full = bars;            // [1]
-    uint64_t* k_full = bars + 1;        // [2]
-    uint64_t* k_empty = bars + 3;       // [2]
-    uint64_t* v_full = bars + 5;        // [2]
-    uint64_t* v_empty = bars + 7;       // [2]
-    uint64_t* s_full = bars + 9;        // [2] one per S buffer
-    uint64_t* p_ready = bars + 11;      // [1] count 128
-    uint64_t* pv_done = bars + 12;      // [2] alternating, so a waiter may lag one PV behind
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
+    uint64_t* k_full = bars + 1;        // [3]
+    uint64_t* k_empty = bars + 4;       // [3]
+    uint64_t* v_full = bars + 7;        // [2]
+    uint64_t* v_empty = bars + 9;       // [2]
+    uint64_t* s_full = bars + 11;       // [2] one per S buffer
+    uint64_t* p_ready = bars + 13;      // [1] count 128
+    uint64_t* pv_done = bars + 14;      // [2] alternating, so a waiter may lag one PV behind
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nqb = gridDim.x;
@@ -75,13 +76,15 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
     const int q0 = qb * ATT_BM;
     const int kv_end = CAUSAL ? min(p.kv_len, q0 + ATT_BM) : p.kv_len;
     const int nblk = (kv_end + ATT_BN - 1) / ATT_BN;
+    const bool ts_on = p.ts != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && ((threadIdx.x & 31) == 0 || (threadIdx.x >> 5) == 1);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
     }
     if (warp == 1 && lane == 0) {
         mbar_init(q_full, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+        for (int i = 0; i < Cfg::K_STAGES; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
         mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(p_ready, 128); mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
         fence_barrier_init();
     }
@@ -96,13 +99,15 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             mbar_expect_tx(q_full, Cfg::Q_BYTES);
 #pragma unroll
             for (int c = 0; c < D / 64; ++c) tma_load_3d(&tmQ, q_full, sQ + c * (ATT_BM * 128), h * D + c * 64, q0, b);
+            int ks = 0; uint32_t kph = 0;
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
-                mbar_wait(&k_empty[st], ph ^ 1);
-                mbar_expect_tx(&k_full[st], Cfg::KV_BYTES);
+                mbar_wait(&k_empty[ks], kph ^ 1);
+                mbar_expect_tx(&k_full[ks], Cfg::KV_BYTES);
 #pragma unroll
                 for (int c = 0; c < D / 64; ++c)
-                    tma_load_3d(&tmK, &k_full[st], sK + st * Cfg::KV_BYTES + c * (ATT_BN * 128), hk * D + c * 64, j * ATT_BN, b);
+                    tma_load_3d(&tmK, &k_full[ks], sK + ks * Cfg::KV_BYTES + c * (ATT_BN * 128), hk * D + c * 64, j * ATT_BN, b);
+                if (++ks == Cfg::K_STAGES) { ks = 0; kph ^= 1; }
                 mbar_wait(&v_empty[st], ph ^ 1);
                 mbar_expect_tx(&v_full[st], Cfg::KV_BYTES);
 #pragma unroll
@@ -111,24 +116,29 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        // The whole warp runs the issue loop (warp-uniform control flow and descriptor arithmetic: no per-lane waterfall loops
+        // around the tcgen05 instructions); one elected lane issues the MMAs and commits.
+        {
+            const bool ldr = elect_one();
             constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, false, false);
             constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, D, false, true);
             const uint32_t tS = tmem_base, tO = tmem_base + Cfg::O_COL;
+            int ks = 0; uint32_t kph = 0;                   // K ring position of the next QK to issue (issued in order)
             auto issue_qk = [&](int j) {
                 const int st = j & 1;
-                mbar_wait(&k_full[st], (j >> 1) & 1);
+                mbar_wait(&k_full[ks], kph);
                 tc_fence_after();
-                const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * Cfg::KV_BYTES);
+                const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + ks * Cfg::KV_BYTES);
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k) {
                     const uint32_t off_q = (k >> 2) * (ATT_BM * 128) + (k & 3) * 32;
                     const uint32_t off_k = (k >> 2) * (ATT_BN * 128) + (k & 3) * 32;
-                    umma_bf16(tS + (uint32_t)(st * ATT_BN), make_smem_desc(qa + off_q, 0, 1024),
-                              make_smem_desc(ka + off_k, 0, 1024), idesc_qk, k > 0 ? 1u : 0u);
+                    if (ldr) umma_bf16(tS + (uint32_t)(st * ATT_BN), make_smem_desc(qa + off_q, 0, 1024),
+                                       make_smem_desc(ka + off_k, 0, 1024), idesc_qk, k > 0 ? 1u : 0u);
                 }
-                umma_commit(&k_empty[st]);
-                umma_commit(&s_full[st]);
+                if (ldr) { umma_commit(&k_empty[ks]); umma_commit(&s_full[st]); }
+                __syncwarp();
+                if (++ks == Cfg::K_STAGES) { ks = 0; kph ^= 1; }
             };
             // S is double-buffered in TMEM and issued two key blocks ahead, so the tensor pipe computes S(j+1) while the
             // softmax threads are still working on S(j); PV(j) (on the critical path to the next P write) goes first.
@@ -139,22 +149,22 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 const int st = j & 1;
                 mbar_wait(p_ready, j & 1);                // P(j) in smem; S buffer j & 1 drained
                 tc_fence_after();
+                if (ldr) ATT_TS(4);
                 mbar_wait(&v_full[st], (j >> 1) & 1);
                 tc_fence_after();
-                const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * Cfg::KV_BYTES);
+                if (ldr) ATT_TS(5);
+                const uint32_t va = smem_u32(sV + st * Cfg::KV_BYTES);
 #pragma unroll
                 for (int k = 0; k < ATT_BN / 16; ++k) {
-                    // A = P [128 x 64] K-major; B = V tile [64 keys x D] stored key-major rows -> MN-major operand
-                    if constexpr (PT)
-                        umma_bf16_ts(tO, tS + (uint32_t)(st * ATT_BN + k * 8),
-                                     make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
-                    else
-                        umma_bf16(tO, make_smem_desc(pa + k * 32, 0, 1024),
-                                  make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
+                    // A = P [128 x 64] from TMEM (bf16 pairs, 8 columns per K=16); B = V tile [64 keys x D], MN-major operand
+                    if (ldr) umma_bf16_ts(tO, tS + (uint32_t)(st * ATT_BN + k * 8),
+                                          make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
                 }
-                umma_commit(&v_empty[st]);
-                umma_commit(&pv_done[j & 1]);
+                if (ldr) { umma_commit(&v_empty[st]); umma_commit(&pv_done[j & 1]); }
+                __syncwarp();
+                if (ldr) ATT_TS(6);
                 if (j + 2 < nblk) issue_qk(j + 2);
+                if (ldr) ATT_TS(7);
             }
         }
     } else if (warp >= 4) {
@@ -167,10 +177,12 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
         for (int j = 0; j < nblk; ++j) {
             mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             tc_fence_after();
+            if (warp == 4) ATT_TS(0);
             uint32_t r0[32], r1[32];
             tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN), r0);
             tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN) + 32, r1);
             tmem_ld_wait();
+            if (warp == 4) ATT_TS(1);
             // raw scores: the softmax scale is folded into the exponent's FMA (max commutes with the positive scale)
             float s[64];
 #pragma unroll
@@ -189,14 +201,10 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             const float mx = fmaxf(mx0, mx1) * p.scale_log2;
             const bool grow = mx > m_used + 8.f;
             const bool any_grow = j > 0 && __any_sync(0xffffffffu, grow);
-            if constexpr (PT) {
-                // P(j) goes to its own S buffer: only a rescale of O needs PV(j-1) retired. PV(j-2) is consumed every
-                // iteration so the parity of each of the two alternating barriers never runs two phases ahead.
-                if (j > 1) mbar_wait(&pv_done[j & 1], ((j - 2) >> 1) & 1);
-                if (any_grow) mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
-            } else {
-                if (j > 0) mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);      // P buffer free again, O accumulator stable
-            }
+            // P(j) goes to its own S buffer: only a rescale of O needs PV(j-1) retired. PV(j-2) is consumed every
+            // iteration so the parity of each of the two alternating barriers never runs two phases ahead.
+            if (j > 1) mbar_wait(&pv_done[j & 1], ((j - 2) >> 1) & 1);
+            if (any_grow) mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
             if (j == 0) {
                 m_used = (mx == -INFINITY) ? 0.f : mx;
             } else if (any_grow) {
@@ -227,18 +235,15 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 uint4 u;
                 u.x = pack_bf16(e[0], e[1]); u.y = pack_bf16(e[2], e[3]); u.z = pack_bf16(e[4], e[5]); u.w = pack_bf16(e[6], e[7]);
                 sum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));      // fp32 row sum (as flash-attn)
-                if constexpr (PT) { pk[c8 * 4] = u.x; pk[c8 * 4 + 1] = u.y; pk[c8 * 4 + 2] = u.z; pk[c8 * 4 + 3] = u.w; }
-                else *reinterpret_cast<uint4*>(sP + row * 128 + ((c8 ^ (row & 7)) << 4)) = u;
+                pk[c8 * 4] = u.x; pk[c8 * 4 + 1] = u.y; pk[c8 * 4 + 2] = u.z; pk[c8 * 4 + 3] = u.w;
             }
             l += sum;
-            if constexpr (PT) {
-                tmem_st32(tS + (uint32_t)((j & 1) * ATT_BN), pk);
-                tmem_st_wait();
-            } else {
-                fence_proxy_async_smem();
-            }
+            if (warp == 4) ATT_TS(2);
+            tmem_st32(tS + (uint32_t)((j & 1) * ATT_BN), pk);
+            tmem_st_wait();
             tc_fence_before();
             mbar_arrive(p_ready);
+            if (warp == 4) ATT_TS(3);
         }
         // ---- epilogue: O / l -> bf16 -> smem (Q region, free: every QK MMA has retired) -> TMA store
         mbar_wait(&pv_done[(nblk - 1) & 1], ((nblk - 1) >> 1) & 1);
@@ -287,8 +292,19 @@ static int att_tmap(CUtensorMap* m, const void* ptr, int cols, int S, int B, int
     return encode_tmap_bf16(m, ptr, 3, dims, strides, box);
 }
 
-template <int D, bool CAUSAL, bool PT>
-static int launch_attn_fwd_impl(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, float* lse, int B,
+// debug timeline buffer (VLB_ATT_TS=1): 64 key blocks x 8 stamps, read back with vlb_attn_debug_ts
+static long long* att_ts_buffer() {
+    static long long* buf = [] {
+        const char* e = getenv("VLB_ATT_TS");
+        long long* b = nullptr;
+        if (e && e[0] == '1') { cudaMalloc(&b, 64 * 8 * sizeof(long long)); cudaMemset(b, 0, 64 * 8 * sizeof(long long)); }
+        return b;
+    }();
+    return buf;
+}
+
+template <int D, bool CAUSAL>
+static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, float* lse, int B,
                            int S, int Hq, int Hkv, float scale, cudaStream_t st) {
     using Cfg = AttCfg<D>;
     CUtensorMap tq, tk, tv, to;
@@ -299,7 +315,8 @@ static int launch_attn_fwd_impl(const void* q, const void* k, const void* v, int
     if ((rc = att_tmap(&to, o, Hq * D, S, B, ld_o, ATT_BM))) return rc;
     AttParams p;
     p.S = S; p.kv_len = S; p.group = Hq / Hkv; p.scale_log2 = scale * 1.4426950408889634f; p.lse = lse; p.Hq = Hq;
-    auto kern = attn_fwd_kernel<D, CAUSAL, PT>;
+    p.ts = att_ts_buffer();
+    auto kern = attn_fwd_kernel<D, CAUSAL>;
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -311,17 +328,15 @@ static int launch_attn_fwd_impl(const void* q, const void* k, const void* v, int
     return check_launch("attn_fwd_kernel");
 }
 
-template <int D, bool CAUSAL>
-static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, float* lse, int B,
-                           int S, int Hq, int Hkv, float scale, cudaStream_t st) {
-    static const bool pt = [] { const char* e = getenv("VLB_ATT_P_TMEM"); return !(e && e[0] == '0'); }();
-    return pt ? launch_attn_fwd_impl<D, CAUSAL, true>(q, k, v, ld_qkv, o, ld_o, lse, B, S, Hq, Hkv, scale, st)
-              : launch_attn_fwd_impl<D, CAUSAL, false>(q, k, v, ld_qkv, o, ld_o, lse, B, S, Hq, Hkv, scale, st);
-}
-
 }  // namespace vlb
 
 using namespace vlb;
+
+extern "C" int vlb_attn_debug_ts(long long* host_out, int n) {
+    long long* b = att_ts_buffer();
+    VLB_REQUIRE(b != nullptr && n <= 64 * 8, "attn_debug_ts: set VLB_ATT_TS=1 (n=%d)", n);
+    return cudaMemcpy(host_out, b, n * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
+}
 
 extern "C" int vlb_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* o, int ld_o, void* lse_f32,
                             int B, int S, int Hq, int Hkv, int D, int causal, float scale, void* stream) {

@@ -127,6 +127,9 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+#ifndef VLB_MBAR_SUSPEND_NS
+#define VLB_MBAR_SUSPEND_NS 0x989680u
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
@@ -134,7 +137,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)      // suspend-time hint: waiting warps sleep instead of polling
+        : "r"(smem_u32(bar)), "r"(parity), "r"(VLB_MBAR_SUSPEND_NS)      // suspend-time hint: waiting warps sleep instead of polling
         : "memory");
     return ok != 0;
 }
