@@ -49,6 +49,7 @@ int vlb_attn_fwd(const void* q, const void* k, const void* v, int ld_qkv, void* 
 /* Debug only (VLB_ATT_TS=1): clock64 stamps of the softmax / MMA-issuer hand-offs of the heaviest forward CTA, 8 per key
  * block (tools/attn_timeline.py). */
 int vlb_attn_debug_ts(long long* host_out, int n);
+int vlb_attn_bwd_debug_ts(long long* host_out, int n);      /* backward: 16 stamps per 64-query step of CTA 0 */
 
 /* Backward (head_dim 128, S % 128 == 0). delta_f32 [B,Hq,S] and dq_f32 [B*S, Hq*D] are caller-provided scratch/outputs
  * (delta_f32 is left holding scale * rowsum(dO o O): the softmax scale travels inside dS);

@@ -60,12 +60,16 @@ struct BwParams {
     int ld_dkv;
     int nkb, nbh;           // key blocks per sequence, Hkv * B
     int chunk;              // batch elements per dispatch chunk
+    int ts_cta;             // which CTA records the timeline (VLB_ATT_TS_CTA, default 0)
+    long long* ts;          // debug (VLB_ATT_TS=1): clock64 stamps of the hand-offs of CTA 0, 16 per step (tools/attn_timeline.py bwd)
     int dbg;                // VLB_BW_DBG timing experiments (bit0: skip dQ reduction, bit1: skip exp2) -- never set in product runs
 };
 
+#define BW_TS(slot) do { if (ts_on && t < 128) p.ts[t * 16 + (slot)] = clock64(); } while (0)
 __global__ void __launch_bounds__(BW_THREADS, 1)
 attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO) {
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                const __grid_constant__ CUtensorMap tmDQ) {
     using Cfg = BwCfg;
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -103,9 +107,10 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
     const int i_start = p.causal ? (k0 / BW_BQ) : 0;
     const int per_head = nq - i_start;
     const int T = p.group * per_head;
+    const bool ts_on = p.ts != nullptr && (int)blockIdx.x == p.ts_cta;
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmDO);
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmDO); tma_prefetch_desc(&tmDQ);
     }
     if (warp == 1 && lane == 0) {
         mbar_init(kv_full, 1);
@@ -148,7 +153,11 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        // The whole warp runs the issue loop (warp-uniform control flow and descriptor arithmetic, so the compiler keeps the
+        // operands in uniform registers instead of wrapping every tcgen05.mma in a per-lane waterfall loop); one elected
+        // lane issues the MMAs and commits.
+        {
+            const bool ldr = elect_one();
             constexpr uint32_t id_s = make_idesc_bf16(128, BW_BQ, false, false);    // (1)(2): A,B K-major
             constexpr uint32_t id_acc = make_idesc_bf16(128, BW_D, false, true);    // (3)(4): A K-major, B MN-major
             constexpr uint32_t id_dq = make_idesc_bf16(128, BW_BQ, true, true);     // (5): A,B MN-major
@@ -162,10 +171,10 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 for (int k = 0; k < BW_D / 16; ++k) {
                     const uint32_t offA = (k >> 2) * (BW_BK * 128) + (k & 3) * 32;
                     const uint32_t offB = (k >> 2) * (BW_BQ * 128) + (k & 3) * 32;
-                    umma_bf16(tmem_base + Cfg::T_S + (t & 1) * BW_BQ, make_smem_desc(ka + offA, 0, 1024),
+                    if (ldr) umma_bf16(tmem_base + Cfg::T_S + (t & 1) * BW_BQ, make_smem_desc(ka + offA, 0, 1024),
                               make_smem_desc(qa + offB, 0, 1024), id_s, k > 0 ? 1u : 0u);
                 }
-                umma_commit(&s_full[t & 1]);
+                if (ldr) umma_commit(&s_full[t & 1]);
             };
             auto issue_dp = [&](int t) {           // (2) dP^T(t); the stage was already waited for by issue_s(t)
                 const uint32_t doa = smem_u32(sDO + (t % BW_NST) * Cfg::QDO_BYTES);
@@ -173,12 +182,11 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                 for (int k = 0; k < BW_D / 16; ++k) {
                     const uint32_t offA = (k >> 2) * (BW_BK * 128) + (k & 3) * 32;
                     const uint32_t offB = (k >> 2) * (BW_BQ * 128) + (k & 3) * 32;
-                    umma_bf16(tmem_base + Cfg::T_DP, make_smem_desc(va + offA, 0, 1024), make_smem_desc(doa + offB, 0, 1024),
+                    if (ldr) umma_bf16(tmem_base + Cfg::T_DP, make_smem_desc(va + offA, 0, 1024), make_smem_desc(doa + offB, 0, 1024),
                               id_s, k > 0 ? 1u : 0u);
                 }
-                umma_commit(dp_full);
+                if (ldr) umma_commit(dp_full);
             };
-            const bool pt = !(p.dbg & 4);
             mbar_wait(kv_full, 0);
             issue_s(0);
             issue_dp(0);
@@ -186,40 +194,38 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
             for (int t = 0; t < T; ++t) {
                 const int st = t % BW_NST;
                 const uint32_t qa = smem_u32(sQ + st * Cfg::QDO_BYTES), doa = smem_u32(sDO + st * Cfg::QDO_BYTES);
-                const uint32_t pa = smem_u32(sP + (t & 1) * Cfg::PS_BYTES), dsa = smem_u32(sDS + (t & 1) * Cfg::PS_BYTES);
+                const uint32_t dsa = smem_u32(sDS + (t & 1) * Cfg::PS_BYTES);
                 mbar_wait(pds_ready, t & 1);       // P/dS(t) in smem / TMEM; S(t), dP(t) TMEM columns drained
                 tc_fence_after();
+                if (ldr) BW_TS(7);
                 if (t + 1 < T) issue_dp(t + 1);
-                if (pt) {
+                if (ldr) BW_TS(8);
+                {
                     // (3)(4) with the A operand from TMEM: P^T / dS^T were packed (bf16 pairs along the query axis) over the
                     // S buffer by the softmax threads -- warpgroup g: P^T at columns 32g..32g+15, dS^T at 32g+16..32g+31
                     const uint32_t ta = tmem_base + Cfg::T_S + (t & 1) * BW_BQ;
 #pragma unroll
                     for (int k = 0; k < BW_BQ / 16; ++k) {
                         const uint32_t ca = (uint32_t)((k >> 1) * 32 + (k & 1) * 8);
-                        umma_bf16_ts(tmem_base + Cfg::T_DV, ta + ca,
+                        if (ldr) umma_bf16_ts(tmem_base + Cfg::T_DV, ta + ca,
                                      make_smem_desc(doa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
-                        umma_bf16_ts(tmem_base + Cfg::T_DK, ta + ca + 16,
+                        if (ldr) umma_bf16_ts(tmem_base + Cfg::T_DK, ta + ca + 16,
                                      make_smem_desc(qa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
                     }
-                } else {
-#pragma unroll
-                    for (int k = 0; k < BW_BQ / 16; ++k) {          // (3) dV += P^T dO ; (4) dK += dS^T Q
-                        umma_bf16(tmem_base + Cfg::T_DV, make_smem_desc(pa + k * 32, 0, 1024),
-                                  make_smem_desc(doa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
-                        umma_bf16(tmem_base + Cfg::T_DK, make_smem_desc(dsa + k * 32, 0, 1024),
-                                  make_smem_desc(qa + k * (16 * 128), BW_BQ * 128, 1024), id_acc, (t > 0 || k > 0) ? 1u : 0u);
-                    }
                 }
+                if (ldr) BW_TS(9);
                 if (t > 0) { mbar_wait(dq_free, (t - 1) & 1); tc_fence_after(); }
+                if (ldr) BW_TS(10);
 #pragma unroll
                 for (int k = 0; k < BW_BK / 16; ++k) {          // (5) dQ^T = K^T dS^T, contraction over the 128 keys
-                    umma_bf16(tmem_base + Cfg::T_DQ, make_smem_desc(ka + k * (16 * 128), BW_BK * 128, 1024),
+                    if (ldr) umma_bf16(tmem_base + Cfg::T_DQ, make_smem_desc(ka + k * (16 * 128), BW_BK * 128, 1024),
                               make_smem_desc(dsa + k * (16 * 128), BW_BK * 128, 1024), id_dq, k > 0 ? 1u : 0u);
                 }
-                umma_commit(&qdo_empty[st]);
-                umma_commit(mma_done);
-                if (t + 2 < T) issue_s(t + 2);     // S buffer t & 1 was drained before pds_ready(t)
+                if (ldr) umma_commit(&qdo_empty[st]);
+                if (ldr) umma_commit(mma_done);
+                if (ldr) BW_TS(11);
+                if (t + 2 < T) issue_s(t + 2);
+                if (ldr) BW_TS(12);     // S buffer t & 1 was drained before pds_ready(t)
             }
         }
     } else if (warp >= 4) {
@@ -229,22 +235,27 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
         const uint32_t tb = tmem_base + ((uint32_t)(qd * 32) << 16);
         const int key = k0 + row;
         const int cb = wg * 32;
-        const bool pt = !(p.dbg & 4);
+        // dQ^T(t) [128 d x 64 q] leaves through shared memory: each thread holds 32 query columns of its d row, writes them
+        // transposed into a plain [64 q][128 d] fp32 tile (a warp stores 32 consecutive floats: conflict-free), and ONE
+        // TMA reduce-add (cp.reduce.async.bulk.tensor ... .add) folds the 32 KB tile into dq -- instead of 32 red.global
+        // instructions per thread, which kept the LSU busy for ~1000 cycles of every 2900-cycle step (timeline r01d).
+        float* stg = reinterpret_cast<float*>(sP);       // the former smem P buffers (P lives in TMEM)
+        const bool red_issuer = (warp == 4 && lane == 0);
         auto drain_dq = [&](int h, int q0) {
-            float* dst = p.dq + ((size_t)b * p.S + q0 + cb) * ((size_t)p.Hq * BW_D) + (size_t)h * BW_D + row;
             uint32_t r[32];
+            if (red_issuer) tma_store_wait_read<0>();    // the previous tile has been read out of the staging buffer
             tmem_ld32(tb + Cfg::T_DQ + cb, r);
             tmem_ld_wait();
             tc_fence_before();
             mbar_arrive(dq_free);                        // registers hold the tile: the next dQ^T MMA may overwrite TMEM
-            if (!(p.dbg & 1)) {
-                if (p.Hq == 32) {                            // Mistral-7B: constant row stride -> immediate address offsets
+            asm volatile("bar.sync 2, 256;" ::: "memory");
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) atomicAdd(dst + c * (32 * BW_D), __uint_as_float(r[c]));
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) atomicAdd(dst + (size_t)c * ((size_t)p.Hq * BW_D), __uint_as_float(r[c]));
-                }
+            for (int c = 0; c < 32; ++c) stg[(cb + c) * BW_D + row] = __uint_as_float(r[c]);
+            fence_proxy_async_smem();
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+            if (red_issuer && !(p.dbg & 1)) {
+                tma_reduce_add_2d(&tmDQ, stg, h * BW_D, b * p.S + q0);
+                tma_store_commit();
             }
         };
         int hh = 0, qi = 0, st = 0, prev_h = 0, prev_q0 = 0;
@@ -252,16 +263,17 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
         for (int t = 0; t < T; ++t) {
             const int q0 = (i_start + qi) * BW_BQ;
             mbar_wait(&qdo_full[st], st_ph);             // lse/delta vectors landed (bulk copies on the same barrier)
+            if (warp == 4 && lane == 0) BW_TS(0);
             const float* lse = sVec + st * 2 * BW_BQ + cb;
             const float* dl = lse + BW_BQ;
             const bool diag = p.causal && (q0 < k0 + BW_BK);      // some (key > query) pairs in this tile
-            uint8_t* pP = sP + (t & 1) * Cfg::PS_BYTES + row * 128;
             uint8_t* pDS = sDS + (t & 1) * Cfg::PS_BYTES + row * 128;
             float pv[32];
             {   // phase A: P^T = exp2(S^T * c - LSE) for this thread's key row and 32 query columns
                 uint32_t rs[32];
                 mbar_wait(&s_full[t & 1], (t >> 1) & 1);
                 tc_fence_after();
+                if (warp == 4 && lane == 0) BW_TS(1);
                 tmem_ld32(tb + Cfg::T_S + (t & 1) * BW_BQ + cb, rs);
                 tmem_ld_wait();
 #pragma unroll
@@ -278,25 +290,17 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
 #pragma unroll
                     for (int c = 0; c < 32; ++c) pv[c] = c < nz ? 0.f : pv[c];
                 }
-                if (pt) {
-                    uint32_t pp[16];
+                uint32_t pp[16];
 #pragma unroll
-                    for (int c = 0; c < 16; ++c) pp[c] = pack_bf16(pv[2 * c], pv[2 * c + 1]);
-                    tmem_st16(tb + Cfg::T_S + (t & 1) * BW_BQ + cb, pp);      // over this thread's own (already read) S columns
-                } else {
-#pragma unroll
-                    for (int c8 = 0; c8 < 4; ++c8) {
-                        uint4 u;
-                        u.x = pack_bf16(pv[c8 * 8 + 0], pv[c8 * 8 + 1]); u.y = pack_bf16(pv[c8 * 8 + 2], pv[c8 * 8 + 3]);
-                        u.z = pack_bf16(pv[c8 * 8 + 4], pv[c8 * 8 + 5]); u.w = pack_bf16(pv[c8 * 8 + 6], pv[c8 * 8 + 7]);
-                        *reinterpret_cast<uint4*>(pP + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;
-                    }
-                }
+                for (int c = 0; c < 16; ++c) pp[c] = pack_bf16(pv[2 * c], pv[2 * c + 1]);
+                tmem_st16(tb + Cfg::T_S + (t & 1) * BW_BQ + cb, pp);      // over this thread's own (already read) S columns
             }
+            if (warp == 4 && lane == 0) BW_TS(2);
             {   // phase B: dS^T = P^T o (dP^T - Delta)
                 uint32_t rp[32];
                 mbar_wait(dp_full, t & 1);
                 tc_fence_after();
+                if (warp == 4 && lane == 0) BW_TS(3);
                 tmem_ld32(tb + Cfg::T_DP + cb, rp);
                 tmem_ld_wait();
                 uint32_t pd[16];
@@ -312,18 +316,19 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                     *reinterpret_cast<uint4*>(pDS + (((wg * 4 + c8) ^ (row & 7)) << 4)) = u;      // B operand of dQ^T
                     pd[c8 * 4] = u.x; pd[c8 * 4 + 1] = u.y; pd[c8 * 4 + 2] = u.z; pd[c8 * 4 + 3] = u.w;
                 }
-                if (pt) {
-                    tmem_st16(tb + Cfg::T_S + (t & 1) * BW_BQ + cb + 16, pd);   // A operand of dK
-                    tmem_st_wait();
-                }
+                tmem_st16(tb + Cfg::T_S + (t & 1) * BW_BQ + cb + 16, pd);   // A operand of dK
+                tmem_st_wait();
             }
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(pds_ready);
+            if (warp == 4 && lane == 0) BW_TS(4);
             if (t > 0) {
                 mbar_wait(mma_done, (t - 1) & 1);        // dQ^T(t-1) complete; P/dS buffer (t-1)&1 free for step t+1
                 tc_fence_after();
+                if (warp == 4 && lane == 0) BW_TS(5);
                 drain_dq(prev_h, prev_q0);
+                if (warp == 4 && lane == 0) BW_TS(6);
             }
             prev_h = hk * p.group + hh; prev_q0 = q0;
             if (++qi == per_head) { qi = 0; ++hh; }
@@ -332,6 +337,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
         mbar_wait(mma_done, (T - 1) & 1);
         tc_fence_after();
         drain_dq(prev_h, prev_q0);
+        if (red_issuer) tma_store_wait_all<0>();
         // ---- epilogue: dV_j, dK_j (the softmax scale is already inside dS^T) -> bf16 -> global rows [b*S + key], head hk; each warpgroup 64 columns
         bf16* dvr = p.dv + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
         bf16* dkr = p.dk + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
@@ -368,6 +374,16 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
     if (warp == 2) { tc_fence_after(); tmem_dealloc<Cfg::TMEM_COLS>(tmem_base); }
 }
 
+static long long* bw_ts_buffer() {
+    static long long* buf = [] {
+        const char* e = getenv("VLB_ATT_TS");
+        long long* b = nullptr;
+        if (e && e[0] == '1') { cudaMalloc(&b, 128 * 16 * sizeof(long long)); cudaMemset(b, 0, 128 * 16 * sizeof(long long)); }
+        return b;
+    }();
+    return buf;
+}
+
 // Delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]; one warp per (row, head), D = 128 -> 4 elements per lane
 __global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dO, int ld, float* __restrict__ delta,
                                   long long rows, int S, int Hq, float scale) {
@@ -394,6 +410,12 @@ static int bw_tmap(CUtensorMap* m, const void* ptr, int cols, int S, int B, int 
 
 using namespace vlb;
 
+extern "C" int vlb_attn_bwd_debug_ts(long long* host_out, int n) {
+    long long* b = vlb::bw_ts_buffer();
+    VLB_REQUIRE(b != nullptr && n <= 128 * 16, "attn_bwd_debug_ts: set VLB_ATT_TS=1 (n=%d)", n);
+    return cudaMemcpy(host_out, b, n * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
+}
+
 extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_qkv, const void* o, const void* d_o,
                             int ld_o, const void* lse_f32, void* delta_f32, void* dq_f32, void* dk, void* dv, int ld_dkv,
                             int B, int S, int Hq, int Hkv, int D, int causal, float scale, void* stream) {
@@ -417,12 +439,21 @@ extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_
     if ((rc = bw_tmap(&tk, k, Hkv * D, S, B, ld_qkv, BW_BK))) return rc;
     if ((rc = bw_tmap(&tv, v, Hkv * D, S, B, ld_qkv, BW_BK))) return rc;
     if ((rc = bw_tmap(&tdo, d_o, Hq * D, S, B, ld_o, BW_BQ))) return rc;
+    CUtensorMap tdq;
+    {   // dq fp32 [B*S, Hq*D]: box = one dQ tile (64 query rows x 128 d), plain layout, target of the TMA reduce-add
+        unsigned long long dims[2] = {(unsigned long long)Hq * D, (unsigned long long)B * S};
+        unsigned long long strides[1] = {(unsigned long long)Hq * D * sizeof(float)};
+        unsigned int box[2] = {(unsigned)BW_D, (unsigned)BW_BQ};
+        if ((rc = encode_tmap_f32_plain(&tdq, dq_f32, 2, dims, strides, box))) return rc;
+    }
     BwParams p;
     p.S = S; p.Hq = Hq; p.Hkv = Hkv; p.group = Hq / Hkv; p.causal = causal;
     p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
     p.lse = (const float*)lse_f32; p.delta = (const float*)delta_f32; p.dq = (float*)dq_f32;
     p.dk = (bf16*)dk; p.dv = (bf16*)dv; p.ld_dkv = ld_dkv;
     { const char* d = getenv("VLB_BW_DBG"); p.dbg = d ? atoi(d) : 0; }
+    p.ts = bw_ts_buffer();
+    { const char* c = getenv("VLB_ATT_TS_CTA"); p.ts_cta = c ? atoi(c) : 0; }
     static bool attr = false;
     if (!attr) {
         e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwCfg::SMEM_BYTES);
@@ -434,6 +465,6 @@ extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_
     // the 126 MB L2 while all key blocks reduce into them; measured at B=8: chunk 1/2/4/8 -> 1.078/1.065/1.071/1.118 ms
     p.chunk = B < 2 ? B : 2;
     dim3 grid((unsigned)(p.nkb * p.nbh));
-    attn_bwd_kernel<<<grid, BW_THREADS, BwCfg::SMEM_BYTES, st>>>(p, tq, tk, tv, tdo);
+    attn_bwd_kernel<<<grid, BW_THREADS, BwCfg::SMEM_BYTES, st>>>(p, tq, tk, tv, tdo, tdq);
     return check_launch("attn_bwd_kernel");
 }

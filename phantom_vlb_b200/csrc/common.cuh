@@ -25,6 +25,9 @@ int num_sms();
 int encode_tmap_bf16(CUtensorMap* out, const void* ptr, int rank, const unsigned long long* dims,
                      const unsigned long long* strides_bytes, const unsigned int* box);
 
+int encode_tmap_f32_plain(CUtensorMap* out, const void* ptr, int rank, const unsigned long long* dims,
+                          const unsigned long long* strides_bytes, const unsigned int* box);
+
 // ---------------------------------------------------------------- bf16 utils
 typedef __nv_bfloat16 bf16;
 typedef __nv_bfloat162 bf162;
@@ -177,6 +180,11 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, const void* smem,
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                  ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem)), "r"(x), "r"(y)
                  : "memory");
+}
+// TMA reduce-add of a shared-memory tile into global memory (element-wise fp32 add done by the copy engine / L2)
+__device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, const void* smem, int x, int y) {
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem)), "r"(x), "r"(y) : "memory");
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // 1-D bulk copy global -> shared (bytes % 16 == 0, both addresses 16-byte aligned), completes on an mbarrier

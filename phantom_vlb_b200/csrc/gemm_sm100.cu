@@ -433,6 +433,25 @@ int encode_tmap_bf16(CUtensorMap* out, const void* ptr, int rank, const unsigned
     return 0;
 }
 
+// fp32, no swizzle: plain row-major boxes (used by the attention backward's TMA reduce-add of dQ tiles)
+int encode_tmap_f32_plain(CUtensorMap* out, const void* ptr, int rank, const unsigned long long* dims,
+                          const unsigned long long* strides_bytes, const unsigned int* box) {
+    PFN_encodeTiled enc = get_encode();
+    VLB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    VLB_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand %p is not 16-byte aligned", ptr);
+    cuuint64_t d[5]; cuuint64_t st[5]; cuuint32_t bx[5]; cuuint32_t es[5];
+    for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+    for (int i = 0; i + 1 < rank; ++i) {
+        st[i] = strides_bytes[i];
+        VLB_REQUIRE(st[i] % 16 == 0, "TMA stride %llu bytes is not a multiple of 16", (unsigned long long)st[i]);
+    }
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    VLB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(f32, rank %d) failed (%d)", rank, (int)r);
+    return 0;
+}
+
 void tmap_cache_clear() {
     std::lock_guard<std::mutex> lk(g_tm_mutex);
     g_tm_cache.clear();
