@@ -30,7 +30,7 @@ constexpr int BW_D = 128;
 constexpr int BW_BK = 128;      // keys per CTA
 constexpr int BW_BQ = 64;       // query rows per inner step
 constexpr int BW_NST = 3;       // Q/dO ring stages
-constexpr int BW_THREADS = 384;
+constexpr int BW_THREADS = 512;      // warp 0 TMA, 1 MMA issuer, 2 TMEM alloc, 4-11 softmax (two warpgroups), 12-15 dQ drain
 
 struct BwCfg {
     static constexpr int KV_BYTES = BW_BK * BW_D * 2;          // 32 KB each
@@ -87,9 +87,9 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
     uint64_t* s_full = bars + 7;         // [2] S^T buffer (t & 1) ready
     uint64_t* dp_full = bars + 9;        // dP^T(t) ready
     uint64_t* pds_ready = bars + 10;     // count 256: P^T, dS^T(t) in smem; S(t) / dP(t) TMEM drained
-    uint64_t* mma_done = bars + 11;      // (3)(4)(5) of a step retired: smem P/dS buffer free, dQ^T readable
-    uint64_t* dq_free = bars + 12;       // count 256: dQ^T TMEM drained
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
+    uint64_t* mma_done = bars + 11;      // [2] alternating: (3)(4)(5) of step t retired -> dS buffer t & 1 free, dQ^T(t) readable
+    uint64_t* dq_free = bars + 13;       // count 128: dQ^T TMEM drained by the drain warpgroup
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // (batch, kv head)-major dispatch keeps the fp32 dQ rows that co-resident CTAs reduce into (4 heads x S x 128 x 4 B
@@ -116,7 +116,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
         mbar_init(kv_full, 1);
         for (int i = 0; i < BW_NST; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1); }
         mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(dp_full, 1);
-        mbar_init(pds_ready, 256); mbar_init(mma_done, 1); mbar_init(dq_free, 256);
+        mbar_init(pds_ready, 256); mbar_init(&mma_done[0], 1); mbar_init(&mma_done[1], 1); mbar_init(dq_free, 128);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
@@ -222,12 +222,52 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
                               make_smem_desc(dsa + k * (16 * 128), BW_BK * 128, 1024), id_dq, k > 0 ? 1u : 0u);
                 }
                 if (ldr) umma_commit(&qdo_empty[st]);
-                if (ldr) umma_commit(mma_done);
+                if (ldr) umma_commit(&mma_done[t & 1]);
                 if (ldr) BW_TS(11);
                 if (t + 2 < T) issue_s(t + 2);
                 if (ldr) BW_TS(12);     // S buffer t & 1 was drained before pds_ready(t)
             }
         }
+    } else if (warp >= 12) {
+        // ------------------------------------------------------------------ dQ drain warpgroup (r01d)
+        // dQ^T(t) [128 d x 64 q] leaves through shared memory: each thread holds the 64 query columns of its d row, writes
+        // them transposed into a plain [64 q][128 d] fp32 tile (a warp stores 32 consecutive floats: conflict-free), and ONE
+        // TMA reduce-add (cp.reduce.async.bulk.tensor ... .add) folds the 32 KB tile into dq. It used to be 32 red.global per
+        // softmax thread (~1000 cycles of every 2900-cycle step, timeline r01d); in its own warpgroup the drain also leaves
+        // the softmax warps' serial chain.
+        const int qd = warp & 3;
+        const int row = qd * 32 + lane;                  // d index
+        const uint32_t tb = tmem_base + ((uint32_t)(qd * 32) << 16);
+        float* stg = reinterpret_cast<float*>(sP);       // the former smem P buffers (P lives in TMEM)
+        const bool red_issuer = (warp == 12 && lane == 0);
+        int hh = 0, qi = 0;
+        for (int t = 0; t < T; ++t) {
+            const int h = hk * p.group + hh;
+            const int q0 = (i_start + qi) * BW_BQ;
+            if (++qi == per_head) { qi = 0; ++hh; }
+            mbar_wait(&mma_done[t & 1], (t >> 1) & 1);
+            tc_fence_after();
+            if (red_issuer) tma_store_wait_read<0>();    // the previous tile has been read out of the staging buffer
+            uint32_t r0[32], r1[32];
+            tmem_ld32(tb + Cfg::T_DQ, r0);
+            tmem_ld32(tb + Cfg::T_DQ + 32, r1);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(dq_free);                        // registers hold the tile: the next dQ^T MMA may overwrite TMEM
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+#pragma unroll
+            for (int c = 0; c < 32; ++c) stg[c * BW_D + row] = __uint_as_float(r0[c]);
+#pragma unroll
+            for (int c = 0; c < 32; ++c) stg[(32 + c) * BW_D + row] = __uint_as_float(r1[c]);
+            fence_proxy_async_smem();
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+            if (red_issuer && !(p.dbg & 1)) {
+                tma_reduce_add_2d(&tmDQ, stg, h * BW_D, b * p.S + q0);
+                tma_store_commit();
+            }
+            if (warp == 12 && lane == 0) BW_TS(6);
+        }
+        if (red_issuer) tma_store_wait_all<0>();
     } else if (warp >= 4) {
         const int qd = warp & 3;                         // TMEM lane quadrant this warp may touch
         const int wg = (warp - 4) >> 2;                  // which 32 of the 64 query columns
@@ -235,30 +275,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
         const uint32_t tb = tmem_base + ((uint32_t)(qd * 32) << 16);
         const int key = k0 + row;
         const int cb = wg * 32;
-        // dQ^T(t) [128 d x 64 q] leaves through shared memory: each thread holds 32 query columns of its d row, writes them
-        // transposed into a plain [64 q][128 d] fp32 tile (a warp stores 32 consecutive floats: conflict-free), and ONE
-        // TMA reduce-add (cp.reduce.async.bulk.tensor ... .add) folds the 32 KB tile into dq -- instead of 32 red.global
-        // instructions per thread, which kept the LSU busy for ~1000 cycles of every 2900-cycle step (timeline r01d).
-        float* stg = reinterpret_cast<float*>(sP);       // the former smem P buffers (P lives in TMEM)
-        const bool red_issuer = (warp == 4 && lane == 0);
-        auto drain_dq = [&](int h, int q0) {
-            uint32_t r[32];
-            if (red_issuer) tma_store_wait_read<0>();    // the previous tile has been read out of the staging buffer
-            tmem_ld32(tb + Cfg::T_DQ + cb, r);
-            tmem_ld_wait();
-            tc_fence_before();
-            mbar_arrive(dq_free);                        // registers hold the tile: the next dQ^T MMA may overwrite TMEM
-            asm volatile("bar.sync 2, 256;" ::: "memory");
-#pragma unroll
-            for (int c = 0; c < 32; ++c) stg[(cb + c) * BW_D + row] = __uint_as_float(r[c]);
-            fence_proxy_async_smem();
-            asm volatile("bar.sync 2, 256;" ::: "memory");
-            if (red_issuer && !(p.dbg & 1)) {
-                tma_reduce_add_2d(&tmDQ, stg, h * BW_D, b * p.S + q0);
-                tma_store_commit();
-            }
-        };
-        int hh = 0, qi = 0, st = 0, prev_h = 0, prev_q0 = 0;
+        int qi = 0, st = 0;
         uint32_t st_ph = 0;
         for (int t = 0; t < T; ++t) {
             const int q0 = (i_start + qi) * BW_BQ;
@@ -298,6 +315,7 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
             if (warp == 4 && lane == 0) BW_TS(2);
             {   // phase B: dS^T = P^T o (dP^T - Delta)
                 uint32_t rp[32];
+                if (t > 1) mbar_wait(&mma_done[t & 1], ((t - 2) >> 1) & 1);      // dS smem buffer t & 1: dK/dQ^T(t-2) have read it
                 mbar_wait(dp_full, t & 1);
                 tc_fence_after();
                 if (warp == 4 && lane == 0) BW_TS(3);
@@ -323,21 +341,11 @@ attn_bwd_kernel(const BwParams p, const __grid_constant__ CUtensorMap tmQ, const
             tc_fence_before();
             mbar_arrive(pds_ready);
             if (warp == 4 && lane == 0) BW_TS(4);
-            if (t > 0) {
-                mbar_wait(mma_done, (t - 1) & 1);        // dQ^T(t-1) complete; P/dS buffer (t-1)&1 free for step t+1
-                tc_fence_after();
-                if (warp == 4 && lane == 0) BW_TS(5);
-                drain_dq(prev_h, prev_q0);
-                if (warp == 4 && lane == 0) BW_TS(6);
-            }
-            prev_h = hk * p.group + hh; prev_q0 = q0;
-            if (++qi == per_head) { qi = 0; ++hh; }
+            if (++qi == per_head) qi = 0;
             if (++st == BW_NST) { st = 0; st_ph ^= 1; }
         }
-        mbar_wait(mma_done, (T - 1) & 1);
+        mbar_wait(&mma_done[(T - 1) & 1], ((T - 1) >> 1) & 1);      // every MMA of this CTA has retired
         tc_fence_after();
-        drain_dq(prev_h, prev_q0);
-        if (red_issuer) tma_store_wait_all<0>();
         // ---- epilogue: dV_j, dK_j (the softmax scale is already inside dS^T) -> bf16 -> global rows [b*S + key], head hk; each warpgroup 64 columns
         bf16* dvr = p.dv + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
         bf16* dkr = p.dk + ((size_t)b * p.S + key) * p.ld_dkv + hk * BW_D;
