@@ -64,9 +64,11 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
     uint64_t* v_full = bars + 7;        // [2]
     uint64_t* v_empty = bars + 9;       // [2]
     uint64_t* s_full = bars + 11;       // [2] one per S buffer
-    uint64_t* p_ready = bars + 13;      // [1] count 128
-    uint64_t* pv_done = bars + 14;      // [2] alternating, so a waiter may lag one PV behind
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
+    uint64_t* p_ready = bars + 13;      // [2] count 128, alternating: a softmax warp may be one key block ahead of its
+                                        //     siblings (it no longer waits for PV(j-1)), and its arrival for block j+1 must
+                                        //     not be counted into block j's phase
+    uint64_t* pv_done = bars + 15;      // [2] alternating, so a waiter may lag one PV behind
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 17);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nqb = gridDim.x;
@@ -85,7 +87,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
         mbar_init(q_full, 1);
         for (int i = 0; i < Cfg::K_STAGES; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
-        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(p_ready, 128); mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
+        mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(&p_ready[0], 128); mbar_init(&p_ready[1], 128); mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
@@ -147,7 +149,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             if (nblk > 1) issue_qk(1);
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1;
-                mbar_wait(p_ready, j & 1);                // P(j) in smem; S buffer j & 1 drained
+                mbar_wait(&p_ready[j & 1], (j >> 1) & 1);  // P(j) in TMEM (over S buffer j & 1)
                 tc_fence_after();
                 if (ldr) ATT_TS(4);
                 mbar_wait(&v_full[st], (j >> 1) & 1);
@@ -242,7 +244,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             tmem_st32(tS + (uint32_t)((j & 1) * ATT_BN), pk);
             tmem_st_wait();
             tc_fence_before();
-            mbar_arrive(p_ready);
+            mbar_arrive(&p_ready[j & 1]);
             if (warp == 4) ATT_TS(3);
         }
         // ---- epilogue: O / l -> bf16 -> smem (Q region, free: every QK MMA has retired) -> TMA store
