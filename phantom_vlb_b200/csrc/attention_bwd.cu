@@ -392,19 +392,23 @@ static long long* bw_ts_buffer() {
     return buf;
 }
 
-// Delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]; one warp per (row, head), D = 128 -> 4 elements per lane
+// Delta[b,h,s] = scale * sum_d dO[b,s,h,d] * O[b,s,h,d]; 16 lanes per (row, head), 8 elements (one 16-byte load of each operand)
+// per lane, so a warp covers two heads of a row = 512 contiguous bytes of o and of dO
 __global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dO, int ld, float* __restrict__ delta,
                                   long long rows, int S, int Hq, float scale) {
-    const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (w >= rows * Hq) return;
-    const long long r = w / Hq; const int h = (int)(w % Hq);
-    const size_t off = (size_t)r * ld + h * BW_D + lane * 4;
-    const uint2 a = *reinterpret_cast<const uint2*>(o + off), g = *reinterpret_cast<const uint2*>(dO + off);
-    const float2 a0 = unpack_bf16(a.x), a1 = unpack_bf16(a.y), g0 = unpack_bf16(g.x), g1 = unpack_bf16(g.y);
-    float s = a0.x * g0.x + a0.y * g0.y + a1.x * g1.x + a1.y * g1.y;
-    s = warp_sum(s);
-    if (lane == 0) delta[((size_t)(r / S) * Hq + h) * S + (r % S)] = s * scale;      // pre-scaled: dS^T leaves phase B as scale * dS^T
+    const long long g = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 4;      // (row, head) index
+    const int sub = threadIdx.x & 15;
+    const bool ok = g < rows * Hq;
+    const long long r = ok ? g / Hq : 0; const int h = ok ? (int)(g % Hq) : 0;
+    const size_t off = (size_t)r * ld + h * BW_D + sub * 8;
+    float a[8], d[8];
+    load8(o + off, a); load8(dO + off, d);
+    float s = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s = fmaf(a[e], d[e], s);
+#pragma unroll
+    for (int m = 8; m > 0; m >>= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
+    if (ok && sub == 0) delta[((size_t)(r / S) * Hq + h) * S + (r % S)] = s * scale;      // pre-scaled: dS^T leaves phase B as scale * dS^T
 }
 
 static int bw_tmap(CUtensorMap* m, const void* ptr, int cols, int S, int B, int ld, int box_rows) {
@@ -433,7 +437,7 @@ extern "C" int vlb_attn_bwd(const void* q, const void* k, const void* v, int ld_
     cudaStream_t st = (cudaStream_t)stream;
     const long long rows = (long long)B * S;
     {
-        const long long threads = rows * Hq * 32;
+        const long long threads = rows * Hq * 16;
         attn_delta_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>((const bf16*)o, (const bf16*)d_o, ld_o,
                                                                              (float*)delta_f32, rows, S, Hq, scale);
         int rc = check_launch("attn_delta_kernel");
