@@ -110,6 +110,29 @@ __device__ __forceinline__ float apply_act(float x, int act) {
     }
 }
 
+// Activation of 8 values with the (kernel-uniform) selector branched ONCE per group: the per-element switch above was
+// if-converted by the compiler into "compute every variant (erff included), then select" -- the ViT fc1 GEMM (quick-GELU
+// epilogue) ran at 200 TF/s instead of ~1000 because of it (r01d, tools/gemm_shapes_in_step.py).
+__device__ __forceinline__ void apply_act8(float (&v)[8], int act) {
+    if (act == ACT_QUICK_GELU) {
+        asm volatile("" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = quick_geluf_(v[j]);
+    } else if (act == ACT_SILU) {
+        asm volatile("" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = siluf_(v[j]);
+    } else if (act == ACT_GELU) {
+        asm volatile("" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = gelu_erff_(v[j]);
+    } else if (act == ACT_SIGMOID) {
+        asm volatile("" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = sigmoidf_(v[j]);
+    }
+}
+
 // ---------------------------------------------------------------- PTX: mbarrier
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -309,10 +309,7 @@ gemm_tcgen05_kernel(const GemmParams p,
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] += b[j];
                         }
-                        if (p.act != ACT_NONE) {
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
-                        }
+                        if (p.act != ACT_NONE) apply_act8(v, p.act);
                         if (p.residual != nullptr && m_ok && n_ok) {
                             float rr[8]; load8(p.residual + (size_t)m * p.ldr + nn, rr);
 #pragma unroll

@@ -133,10 +133,7 @@ __global__ void __launch_bounds__(THREADS) layernorm_fwd_kernel(const bf16* __re
 #pragma unroll
                 for (int j = 0; j < 8; ++j) o[j] = bf2f(f2bf(o[j])) + r[j];
             }
-            if (act != ACT_NONE) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] = apply_act(o[j], act);
-            }
+            if (act != ACT_NONE) apply_act8(o, act);
             store8(y + row * H + c * 8, o);
         }
     }
