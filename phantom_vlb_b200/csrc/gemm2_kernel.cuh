@@ -273,24 +273,33 @@ gemm2_tcgen05_kernel(const GemmParams p,
                 for (int h = 0; h < 2; ++h) {
                     uint32_t r[32];
                     const int c0 = s * 64 + h * 32;
-                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + c0), r);
-                    tmem_ld_wait();
                     const int n = n0 + c0;
+                    // bias / residual for these 32 columns are requested BEFORE the TMEM wait: issued inside the per-chunk loop
+                    // each load sat behind the previous chunk's math and exposed a full memory latency
+                    uint4 bv[4], rv[4];
+                    const bool has_bias = p.bias != nullptr, has_res = p.residual != nullptr && m_ok;
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
+                        const int nn = n + c * 8;
+                        bv[c] = (has_bias && nn < p.N) ? __ldg(reinterpret_cast<const uint4*>(p.bias + nn)) : make_uint4(0u, 0u, 0u, 0u);
+                        rv[c] = (has_res && nn < p.N) ? *reinterpret_cast<const uint4*>(p.residual + (size_t)m * p.ldr + nn)
+                                                      : make_uint4(0u, 0u, 0u, 0u);
+                    }
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + c0), r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {           // 4 chunks of 8 columns (16 B of bf16)
                         float v[8];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
-                        const int nn = n + c * 8;
-                        const bool n_ok = nn < p.N;
-                        if (p.bias != nullptr && n_ok) {
-                            float b[8]; load8(p.bias + nn, b);
+                        if (has_bias) {
+                            float b[8]; unpack8(bv[c], b);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] += b[j];
                         }
                         if (p.act != ACT_NONE) apply_act8(v, p.act);
-                        if (p.residual != nullptr && m_ok && n_ok) {
-                            float rr[8]; load8(p.residual + (size_t)m * p.ldr + nn, rr);
+                        if (has_res) {
+                            float rr[8]; unpack8(rv[c], rr);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] = bf2f(f2bf(v[j])) + rr[j];
                         }
