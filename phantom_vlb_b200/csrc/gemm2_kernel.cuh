@@ -9,7 +9,7 @@
 //   full[s]   (leader only)  1 arrival (leader producer's expect_tx of BOTH CTAs' bytes) + TMA complete_tx from both CTAs
 //   empty[s]  (both)         tcgen05.commit multicast from the leader's MMA thread
 //   tfull[a]  (both)         tcgen05.commit multicast
-//   tempty[a] (leader only)  256 arrivals: the 128 epilogue threads of each CTA (remote mbarrier.arrive from the peer)
+//   tempty[a] (leader only)  one arrival per epilogue thread of BOTH CTAs (512 in the plain variant, 256 in the SwiGLU ones; remote mbarrier.arrive from the peer)
 #pragma once
 
 namespace vlb {
@@ -30,8 +30,12 @@ constexpr int G2_TMEM_COLS = 512;
 // SWIGLU == 2 (backward of the down projection, N = I): the accumulator is d(act); the epilogue reads gate/up of its row
 // from gu [M, 2I] and writes dgu = [d(act) up silu'(gate) | d(act) silu(gate)] at column offsets n and I + n (I % 256 == 0),
 // so d(act) never goes to memory and the separate SwiGLU backward pass (read 3I, write 2I per token) disappears.
+// The plain variant (SWIGLU == 0) runs EIGHT epilogue warps (384 threads): two warpgroups, each owning 128 of the tile's 256
+// columns with its own staging buffer, named barrier and TMA-store issuer. With four warps the K = 1024 ViT GEMMs whose
+// epilogue carries an activation or a residual were epilogue-bound (fc1 650, o-proj 500 TF/s against 1350 plain).
+template <int SWIGLU> __host__ __device__ constexpr int g2_threads() { return SWIGLU == 0 ? 384 : 256; }
 template <bool B_MN, int SWIGLU = 0>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2_threads<SWIGLU>(), 1)
 gemm2_tcgen05_kernel(const GemmParams p,
                      const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
@@ -62,7 +66,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 256); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 2 * (g2_threads<SWIGLU>() - 128)); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc_2sm<G2_TMEM_COLS>(tmem_ptr);
@@ -135,9 +139,9 @@ gemm2_tcgen05_kernel(const GemmParams p,
         // ------------------------------------------------------------------ epilogue (128 threads per CTA, own 128 rows)
         const int q = warp & 3;
         const int row = q * 32 + lane;
+        const int wg = (warp - 4) >> 2;                     // epilogue warpgroup (always 0 in the 256-thread SwiGLU variants)
         int it = 0;
-        uint32_t cd_idx = 0;
-        const bool issuer = (warp == 4 && lane == 0);
+        const bool issuer = (q == 0 && lane == 0);          // one TMA-store issuer per warpgroup
         for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
             int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb);
             const int m0 = mb * (2 * BM) + (int)rank * BM, n0 = nb * G2_BN;
@@ -264,11 +268,12 @@ gemm2_tcgen05_kernel(const GemmParams p,
                 }
                 continue;
             }
+            uint8_t* cd = smem_cd + wg * CD_STAGE_BYTES;      // this warpgroup's staging buffer
 #pragma unroll 1
-            for (int s = 0; s < G2_BN / 64; ++s, ++cd_idx) {
-                uint8_t* cd = smem_cd + (cd_idx & 1) * CD_STAGE_BYTES;
-                if (issuer) tma_store_wait_read<1>();
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+            for (int sl = 0; sl < G2_BN / 128; ++sl) {
+                const int s = wg * (G2_BN / 128) + sl;        // 64-column chunk index inside the tile
+                if (issuer) tma_store_wait_read<0>();
+                asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     uint32_t r[32];
@@ -310,12 +315,12 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         *reinterpret_cast<uint4*>(cd + row * 128 + ((chunk ^ (row & 7)) << 4)) = u;
                     }
                 }
-                if (s == G2_BN / 64 - 1) {                  // this CTA's TMEM reads of the accumulator stage are done
+                if (sl == G2_BN / 128 - 1) {                // this thread's TMEM reads of the accumulator stage are done
                     tc_fence_before();
                     mbar_arrive_cluster(&tempty_bar[as], 0);
                 }
                 fence_proxy_async_smem();
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
                 if (issuer) {
                     tma_store_2d(&tmC, cd, n0 + s * 64, m0);
                     tma_store_commit();

@@ -600,7 +600,7 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     int cap = (a.max_ctas > 0 ? a.max_ctas : num_sms()) / 2;
     if (pairs > cap) pairs = cap;
     if (pairs < 1) pairs = 1;
-    kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC, tAct);
+    kern<<<2 * pairs, g2_threads<SWIGLU>(), G2_SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC, tAct);
     return check_launch("gemm2_tcgen05_kernel");
 }
 
