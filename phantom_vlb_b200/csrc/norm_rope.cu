@@ -49,26 +49,36 @@ __global__ void __launch_bounds__(THREADS) rmsnorm_fwd_kernel(const bf16* __rest
 
 // dx = dres + rstd * (g - xhat * mean(g * xhat)),  g = dy * w,  xhat = x * rstd      (w frozen: no dw)
 template <int THREADS, int MAXV>
-__global__ void __launch_bounds__(THREADS) rmsnorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+__global__ void __launch_bounds__(THREADS, 768 / THREADS) rmsnorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
                                                               const bf16* __restrict__ w, const float* __restrict__ rstd_in,
                                                               const bf16* __restrict__ dres, bf16* __restrict__ dx, int H) {
     __shared__ float red[32];
     const size_t row = blockIdx.x;
     const float rstd = rstd_in[row];
-    float g[MAXV][8], xh[MAXV][8], rs[MAXV][8];
+    // the row stays in registers as packed bf16 (48 instead of 96 registers at H=4096: more rows in flight per SM); the
+    // second pass redoes the same fp32 products, so the result is bit-identical to holding them in fp32
+    uint4 gq[MAXV], xq[MAXV], rq[MAXV];
     float dot = 0.f;
     const int nchunk = H / 8;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
         const int c = threadIdx.x + i * THREADS;
         if (c < nchunk) {
-            float wv[8];
-            load8(dy + row * H + c * 8, g[i]);
-            load8(x + row * H + c * 8, xh[i]);
-            if (dres) load8(dres + row * H + c * 8, rs[i]);      // issued before the row reduction, not after it
-            load8(w + c * 8, wv);
+            gq[i] = *reinterpret_cast<const uint4*>(dy + row * H + c * 8);
+            xq[i] = *reinterpret_cast<const uint4*>(x + row * H + c * 8);
+            if (dres) rq[i] = *reinterpret_cast<const uint4*>(dres + row * H + c * 8);   // issued before the row reduction
+        }
+    }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { g[i][j] *= wv[j]; xh[i][j] *= rstd; dot += g[i][j] * xh[i][j]; }
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = threadIdx.x + i * THREADS;
+        if (c < nchunk) {
+            float wv[8], g[8], xh[8];
+            load8(w + c * 8, wv);
+            unpack8(gq[i], g);
+            unpack8(xq[i], xh);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { g[j] *= wv[j]; xh[j] *= rstd; dot += g[j] * xh[j]; }
         }
     }
     dot = block_sum(dot, red) / (float)H;
@@ -76,12 +86,17 @@ __global__ void __launch_bounds__(THREADS) rmsnorm_bwd_kernel(const bf16* __rest
     for (int i = 0; i < MAXV; ++i) {
         const int c = threadIdx.x + i * THREADS;
         if (c < nchunk) {
-            float o[8];
+            float wv[8], g[8], xh[8], o[8];
+            load8(w + c * 8, wv);
+            unpack8(gq[i], g);
+            unpack8(xq[i], xh);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
+            for (int j = 0; j < 8; ++j) { g[j] *= wv[j]; xh[j] *= rstd; o[j] = rstd * (g[j] - xh[j] * dot); }
             if (dres) {
+                float rs[8];
+                unpack8(rq[i], rs);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] += rs[i][j];
+                for (int j = 0; j < 8; ++j) o[j] += rs[j];
             }
             store8(dx + row * H + c * 8, o);
         }
