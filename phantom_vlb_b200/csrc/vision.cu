@@ -121,33 +121,62 @@ __global__ void drop_cls_kernel(const bf16* __restrict__ in, bf16* __restrict__ 
     }
 }
 
-// depthwise 3x3, stride 1, pad 1, no bias; NHWC x [F, Hh, Ww, C]; w packed [9, C] (tap-major)
-__global__ void dwconv3x3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ y,
-                                 long long F, int Hh, int Ww, int C) {
+// depthwise 3x3, stride 1, pad 1, no bias; NHWC x [F, Hh, Ww, C]; w packed [9, C] (tap-major).
+// One thread per (frame, output row, 8 channels) walks along x with the 3x3 window held in registers as packed bf16:
+// 3 new 16-byte loads per output instead of 9 (the one-pixel-per-thread version was L2-bandwidth bound at 9x the
+// algorithmic reads: adjacent threads are adjacent CHANNELS, so no neighbour load ever hit L1). Taps are accumulated in
+// the same (dy, dx) order; out-of-image taps enter as zeros.
+__global__ void __launch_bounds__(128, 4) dwconv3x3_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                        bf16* __restrict__ y, long long F, int Hh, int Ww, int C) {
     const int cpr = C / 8;
-    const long long total = F * Hh * Ww * (long long)cpr;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(i % cpr);
-        const long long pix = i / cpr;
-        const int xx = (int)(pix % Ww), yy = (int)((pix / Ww) % Hh);
-        const long long f = pix / ((long long)Ww * Hh);
+    const long long total = F * Hh * (long long)cpr;
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int c = (int)(i % cpr);
+    const long long row = i / cpr;
+    const int yy = (int)(row % Hh);
+    const long long f = row / Hh;
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    uint4 wq[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) wq[t] = *reinterpret_cast<const uint4*>(w + (size_t)t * C + c * 8);
+    const bf16* rp[3];
+    bool ok[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const int y2 = yy + d - 1;
+        ok[d] = y2 >= 0 && y2 < Hh;
+        rp[d] = x + ((f * Hh + (ok[d] ? y2 : yy)) * Ww) * (long long)C + c * 8;
+    }
+    uint4 left[3], mid[3], right[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        left[d] = zero;
+        mid[d] = ok[d] ? *reinterpret_cast<const uint4*>(rp[d]) : zero;
+    }
+    bf16* yp = y + ((f * Hh + yy) * Ww) * (long long)C + c * 8;
+    for (int xx = 0; xx < Ww; ++xx) {
+        const bool more = xx + 1 < Ww;
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+            right[d] = (ok[d] && more) ? *reinterpret_cast<const uint4*>(rp[d] + (long long)(xx + 1) * C) : zero;
         float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
-        for (int dy = -1; dy <= 1; ++dy) {
-            const int y2 = yy + dy;
-            if (y2 < 0 || y2 >= Hh) continue;
+        for (int d = 0; d < 3; ++d) {
+            float xv[8], wv[8];
+            unpack8(left[d], xv); unpack8(wq[d * 3 + 0], wv);
 #pragma unroll
-            for (int dx = -1; dx <= 1; ++dx) {
-                const int x2 = xx + dx;
-                if (x2 < 0 || x2 >= Ww) continue;
-                float xv[8], wv[8];
-                load8(x + ((f * Hh + y2) * Ww + x2) * (long long)C + c * 8, xv);
-                load8(w + (size_t)((dy + 1) * 3 + (dx + 1)) * C + c * 8, wv);
+            for (int j = 0; j < 8; ++j) acc[j] += xv[j] * wv[j];
+            unpack8(mid[d], xv); unpack8(wq[d * 3 + 1], wv);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[j] += xv[j] * wv[j];
-            }
+            for (int j = 0; j < 8; ++j) acc[j] += xv[j] * wv[j];
+            unpack8(right[d], xv); unpack8(wq[d * 3 + 2], wv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += xv[j] * wv[j];
         }
-        store8(y + pix * C + c * 8, acc);
+        store8(yp + (long long)xx * C, acc);
+#pragma unroll
+        for (int d = 0; d < 3; ++d) { left[d] = mid[d]; mid[d] = right[d]; }
     }
 }
 
@@ -321,7 +350,9 @@ extern "C" int vlb_drop_cls(const void* in, void* out, long long N, int T, int H
 
 extern "C" int vlb_dwconv3x3(const void* x, const void* w9c, void* y, long long F, int Hh, int Ww, int C, void* stream) {
     VLB_REQUIRE(C % 8 == 0, "dwconv3x3: C=%d", C);
-    dwconv3x3_kernel<<<grid_for(F * Hh * Ww * (long long)(C / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+    VLB_REQUIRE(F > 0 && Hh > 0 && Ww > 0, "dwconv3x3: F=%lld Hh=%d Ww=%d", F, Hh, Ww);
+    const long long threads = F * Hh * (long long)(C / 8);
+    dwconv3x3_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
         (const bf16*)x, (const bf16*)w9c, (bf16*)y, F, Hh, Ww, C);
     return check_launch("dwconv3x3");
 }

@@ -160,3 +160,22 @@ def test_uint8_frames_normalised_in_gather_bit_exact():
     b = ops.patch_im2col(frames.cuda().contiguous(), 14, kpad)
     torch.cuda.synchronize()
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("F,Hh,Ww,C", [(3, 24, 24, 256), (2, 13, 13, 64), (1, 1, 1, 8), (2, 1, 5, 16), (2, 5, 1, 16),
+                                        (1, 2, 2, 24)])
+def test_dwconv3x3_matches_torch_grouped_conv(F, Hh, Ww, C):
+    """STC RegStage depthwise 3x3 (timm Bottleneck conv2 with group width 1, projector.py:153-161): NHWC rows, tap-major
+    weights, zero padding. fp32 torch conv on the same bf16 inputs; the only difference allowed is the bf16 rounding of the
+    output (and fp32 summation order)."""
+    from phantom_vlb_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(7)
+    x = torch.randn(F * Hh * Ww, C, device="cuda", generator=g).bfloat16()
+    w = torch.randn(9, C, device="cuda", generator=g).bfloat16()
+    y = ops.dwconv3x3(x, w, F, Hh, Ww)
+    xt = x.float().view(F, Hh, Ww, C).permute(0, 3, 1, 2)
+    wt = w.float().t().reshape(C, 1, 3, 3)
+    ref = torch.nn.functional.conv2d(xt, wt, padding=1, groups=C).permute(0, 2, 3, 1).reshape(F * Hh * Ww, C)
+    err = (y.float() - ref).abs()
+    tol = ref.abs() * 2.0 ** -7 + 1e-5          # one bf16 ulp of the result + fp32 reassociation noise
+    assert bool((err <= tol).all()), float((err - tol).max())
