@@ -43,6 +43,12 @@ def visual_token_lags(num_frames, delay=3, window=3, tr=1.49):
     return tr * (abs_tr_delay - np.arange(0, window + step, step))[:tp]
 
 
+def tr_mid_time(row, delay=3, window=3, tr=1.49):
+    """src/preprocessing/videollama2_vlb_lazyloading.py:99: time stamp (s) of aligned row `row`'s target TR, assigned to the
+    middle of the BOLD slice."""
+    return ((window - 1) + delay + 0.5 + row) * tr
+
+
 def bold_alignment(n_feat_rows, n_bold_rows, delay=3, window=3):
     """src/preprocessing/videollama2_vlb_lazyloading.py:97-130: features[(window-1):], bold[(window-1)+delay:],
     n_rows = min of both -> (first feature row, first bold row, n_rows)."""

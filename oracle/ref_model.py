@@ -15,11 +15,19 @@ CPU fp32 restatement of the phantom_vlb training-step hot path, assembled from
       HRFConvolveLayer / RidgeRegressionLayer src/utils.py:40-73
       make_weight_mask / forward / training_step   src/litmodule/videollama2_vlb_litmodule.py:178-203, 229-256, 259-306
       Pearson r (torchmetrics PearsonCorrCoef after nan_to_num)  src/utils.py:101-110
-PARITY PINNING: the reference ships no golden vectors or tests for this path.  The pieces that
-are reference-owned code (src/utils.py layers, STCConnector glue, multimodal splice, make_weight_mask) are checked
-against the reference files themselves by oracle/make_goldens.py (run in the build container, where /root/reference
-exists) and frozen into tests/golden/*.npz; timm/peft/torchmetrics arithmetic is restated from their published
-behaviour and is "parity unpinned" (packages absent here).
+PARITY PINNING: the reference ships no golden vectors or tests for this path, so the oracle is pinned
+against the reference EXECUTED in the build container by oracle/make_goldens.py (fixtures frozen under tests/golden/):
+  backbone_ref.npz   Videollama2MistralForCausalLM.forward(input_ids, attention_mask, output_hidden_states=True, images=...)
+                     exactly as litmodule.py:231-236 calls it, + encode_images_or_videos, prepare_inputs_labels_for_multimodal
+                     (splice + left-extended attention mask) and CLIPVisionTower.forward, on seeded weights
+                     -> RefVLB.encode_frames / encode_videos / splice / backbone          (tests/test_oracle_cpu.py)
+  stc_connector.npz  STCConnector (projector.py:133-215) with the restated timm stage injected
+  head_utils.npz     HRFConvolveLayer / RidgeRegressionLayer (src/utils.py:40-73)
+  weight_mask.npz    VLBLitModule.make_weight_mask (litmodule.py:178-203)
+  frame_sample.npz, video_chunks.npz, lazyload_align.npz   the integer indexing contract (oracle/indexing.py)
+Still "parity unpinned" (third-party packages absent here, restated from their published behaviour): timm RegStage internals
+(oracle/stc_timm.py), peft lora.Linear, torchmetrics PearsonCorrCoef (checked against numpy), nilearn's Glover regressor
+(oracle/glover.py).
 """
 import math
 from dataclasses import dataclass, field
@@ -205,6 +213,7 @@ class RefVLB(nn.Module):
         B, T = vision.shape[:2]
         feats = self.encode_frames(vision.reshape(B * T, *vision.shape[2:]))
         feats = feats.view(B, T, feats.shape[1], feats.shape[2])
+        self.last_frame_feats = feats.detach()          # per-stage parity checks (tests only)
         return self.mm_projector(feats)
 
     # ---- videollama2_arch.py:161-263 (one <video> per sample, equal lengths -> no re-padding branch)
@@ -273,10 +282,52 @@ class RefVLB(nn.Module):
         pred, l2, pooled, hrf = self.head(hidden, wm)
         loss = F.mse_loss(pred, y) + l2
         return dict(loss=loss, pred=pred, l2=l2, hidden=hidden, mm=mm, embeds=embeds, weight_mask=wm, pooled=pooled,
-                    hrf=hrf)
+                    hrf=hrf, frame_feats=self.last_frame_feats, input_ids=ids)
 
     def trainable(self):
         return [(n, p) for n, p in self.named_parameters() if p.requires_grad]
+
+
+def canonical_params(model: RefVLB):
+    """{VideoLLaMA2 checkpoint key: tensor} for the backbone of a RefVLB -- the names Videollama2MistralForCausalLM's
+    state_dict uses (videollama2_mistral.py:47-61, videollama2_arch.py:31-37, encoder.py:12-29)."""
+    out = {}
+    for k, v in model.vision_tower.state_dict().items():
+        out["model.vision_tower.vision_tower." + k] = v
+    for k, v in model.mm_projector.state_dict().items():
+        out["model.mm_projector." + k] = v
+    for k, v in model.llm.state_dict().items():
+        if "lora_" not in k:
+            out["model." + k.replace(".base_layer.", ".")] = v
+    return out
+
+
+def seed_weights_(named, seed=1234):
+    """Deterministic values for a {key: tensor} map, a function of (seed, key, shape) only -- so the reference model (built in
+    the container by oracle/make_goldens.py) and a RefVLB (built anywhere) hold identical weights without shipping them."""
+    import zlib
+    with torch.no_grad():
+        for k in sorted(named):
+            v = named[k]
+            g = torch.Generator().manual_seed(seed * 1000003 + zlib.crc32(k.encode()))
+            r = torch.randn(v.shape, generator=g)
+            if v.dim() >= 2 or k.endswith("class_embedding"):
+                v.copy_(r * 0.08)
+            elif k.endswith("weight"):
+                v.copy_(1.0 + 0.1 * r)          # norm scales
+            else:
+                v.copy_(0.05 * r)               # biases
+    return named
+
+
+def round_weights_to_bf16(model: RefVLB):
+    """Make every parameter bf16-representable (values only; arithmetic stays fp32). The reference loads its backbone with
+    torch_dtype=bfloat16 (litmodule.py:74-82) and builds the head with dtype=bfloat16 (:217-226), so "identical weights"
+    for a parity run means weights both sides can hold exactly."""
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(p.bfloat16().float())
+    return model
 
 
 def enable_training(model: RefVLB):

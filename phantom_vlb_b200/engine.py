@@ -342,7 +342,7 @@ class Engine:
         wm = ops.weight_mask(batch["padvals"].contiguous(), batch["vis_weights"].contiguous(),
                              batch["lang_weights"].contiguous(), cfg.tok_per_frame, cfg.max_len)
         self.launches += 4
-        self.vis_tokens, self.embeds = vis, x0
+        self.vis_tokens, self.embeds, self.frame_feats, self.weight_mask = vis, x0, feats, wm
         hidden = self.decoder_forward(x0, B, save=save)
         return hidden, wm
 
@@ -451,6 +451,7 @@ class Engine:
         self.drop_step += 1          # fresh LoRA dropout masks every training step (same masks in its backward)
         self._zero_grads()
         hidden, wm = self.backbone_forward(batch, save=lora)
+        self.hidden_pre_norm = hidden
         y = batch["timeseries"].contiguous()
         out, pred = self.head_forward(hidden, wm, y, B, training=True)
         dx = self.head_backward(hidden, wm, B, need_dx=lora)

@@ -136,63 +136,20 @@ def _flatten(d):
 
 
 # ------------------------------------------------------------------------------------------------ from the oracle
-def _stc_block_from(block, dev):
-    C = block.conv1.conv.weight.shape[0]
-    d = dict(
-        conv1_w=_bf(block.conv1.conv.weight.reshape(C, -1), dev), n1_w=_bf(block.conv1.bn.weight, dev), n1_b=_bf(block.conv1.bn.bias, dev),
-        dw_w=_bf(block.conv2.conv.weight.reshape(C, 9).t(), dev), n2_w=_bf(block.conv2.bn.weight, dev), n2_b=_bf(block.conv2.bn.bias, dev),
-        se1_w=_bf(block.se.fc1.weight.reshape(block.se.fc1.weight.shape[0], C), dev), se1_b=_bf(block.se.fc1.bias, dev),
-        se2_w=_bf(block.se.fc2.weight.reshape(C, -1), dev), se2_b=_bf(block.se.fc2.bias, dev),
-        conv3_w=_bf(block.conv3.conv.weight.reshape(C, C), dev), n3_w=_bf(block.conv3.bn.weight, dev), n3_b=_bf(block.conv3.bn.bias, dev),
-        ds_w=None)
-    if hasattr(block.downsample, "conv"):
-        d.update(ds_w=_bf(block.downsample.conv.weight.reshape(C, -1), dev), dsn_w=_bf(block.downsample.bn.weight, dev),
-                 dsn_b=_bf(block.downsample.bn.bias, dev))
-    return d
+def oracle_state_dict(ref):
+    """state_dict of an oracle RefVLB under the key names a VideoLLaMA2 checkpoint uses (weights.py docstring)."""
+    sd = {"model.vision_tower.vision_tower." + k: v for k, v in ref.vision_tower.state_dict().items()}
+    sd.update({"model.mm_projector." + k: v for k, v in ref.mm_projector.state_dict().items()})
+    sd.update({"model." + k: v for k, v in ref.llm.state_dict().items() if "lora_" not in k})
+    return sd
 
 
 def frozen_from_oracle(ref, cfg, dev):
-    """Convert an oracle RefVLB (HF CLIP / Mistral modules + restated STC) into kernel layouts. Test-side helper: the
-    oracle object is passed in, this module never imports it."""
-    W = FrozenWeights()
-    vm = ref.vision_tower.vision_model
-    emb = vm.embeddings
-    pw = emb.patch_embedding.weight.detach().reshape(cfg.vit_hidden, -1)
-    pwp = torch.zeros(cfg.vit_hidden, cfg.kpad)
-    pwp[:, :pw.shape[1]] = pw
-    W.vit = dict(patch_w=_bf(pwp, dev), cls=_bf(emb.class_embedding, dev), pos=_bf(emb.position_embedding.weight, dev),
-                 pre_w=_bf(vm.pre_layrnorm.weight, dev), pre_b=_bf(vm.pre_layrnorm.bias, dev))
-    for i in range(cfg.vit_used_layers):
-        l = vm.encoder.layers[i]
-        a = l.self_attn
-        W.vit_layers.append(dict(
-            ln1_w=_bf(l.layer_norm1.weight, dev), ln1_b=_bf(l.layer_norm1.bias, dev),
-            wqkv=_bf(torch.cat([a.q_proj.weight, a.k_proj.weight, a.v_proj.weight], 0), dev),
-            bqkv=_bf(torch.cat([a.q_proj.bias, a.k_proj.bias, a.v_proj.bias], 0), dev),
-            wo=_bf(a.out_proj.weight, dev), bo=_bf(a.out_proj.bias, dev),
-            ln2_w=_bf(l.layer_norm2.weight, dev), ln2_b=_bf(l.layer_norm2.bias, dev),
-            fc1_w=_bf(l.mlp.fc1.weight, dev), fc1_b=_bf(l.mlp.fc1.bias, dev),
-            fc2_w=_bf(l.mlp.fc2.weight, dev), fc2_b=_bf(l.mlp.fc2.bias, dev)))
-    P = ref.mm_projector
-    C = cfg.hidden
-    W.stc = dict(
-        s1=[_stc_block_from(b, dev) for b in P.s1.children()],
-        s2=[_stc_block_from(b, dev) for b in P.s2.children()],
-        sampler_w=_bf(P.sampler[0].weight.permute(0, 2, 3, 4, 1).reshape(C, 8 * C), dev), sampler_b=_bf(P.sampler[0].bias, dev),
-        ro1_w=_bf(P.readout[0].weight, dev), ro1_b=_bf(P.readout[0].bias, dev),
-        ro2_w=_bf(P.readout[2].weight, dev), ro2_b=_bf(P.readout[2].bias, dev))
-    W.llm = dict(embed=_bf(ref.llm.embed_tokens.weight, dev), norm_w=_bf(ref.llm.norm.weight, dev))
-    W.llm["cos"], W.llm["sin"] = rope_tables(cfg, dev)
-    for l in ref.llm.layers:
-        a, m = l.self_attn, l.mlp
-        W.llm_layers.append(dict(
-            ln1_w=_bf(l.input_layernorm.weight, dev),
-            wqkv=_bf(torch.cat([a.q_proj.base_layer.weight, a.k_proj.base_layer.weight, a.v_proj.base_layer.weight], 0), dev),
-            wo=_bf(a.o_proj.base_layer.weight, dev),
-            ln2_w=_bf(l.post_attention_layernorm.weight, dev),
-            wgu=_bf(torch.cat([m.gate_proj.base_layer.weight, m.up_proj.base_layer.weight], 0), dev),
-            wd=_bf(m.down_proj.base_layer.weight, dev)))
-    return W
+    """Convert an oracle RefVLB (HF CLIP / Mistral modules + restated STC) into kernel layouts through the same key-name
+    path a real checkpoint takes (weights.load_frozen). Test-side helper: the oracle object is passed in, this module
+    never imports it."""
+    from .weights import load_frozen
+    return load_frozen(oracle_state_dict(ref), cfg, dev)
 
 
 # ------------------------------------------------------------------------------------------------ random init (benchmarks)

@@ -17,7 +17,7 @@ def to_dev(batch):
 
 
 def build(cfg_ref, B, seed=1234):
-    from oracle.ref_model import RefVLB, enable_training, synthetic_batch
+    from oracle.ref_model import RefVLB, enable_training, round_weights_to_bf16, synthetic_batch
     from phantom_vlb_b200.engine import Engine
     from phantom_vlb_b200.model import ModelConfig, Trainables, frozen_from_oracle
     ref = enable_training(RefVLB(cfg_ref, seed=seed))
@@ -27,6 +27,7 @@ def build(cfg_ref, B, seed=1234):
         ref.layer_norm1.bias.add_(0.1 * torch.randn(cfg_ref.hidden, generator=g))
         ref.layer_norm2.weight.add_(0.1 * torch.randn(cfg_ref.hidden, generator=g))
         ref.layer_norm2.bias.add_(0.1 * torch.randn(cfg_ref.hidden, generator=g))
+    round_weights_to_bf16(ref)       # identical weights on both sides: the reference holds them in bf16 (litmodule.py:74-82)
     batch = synthetic_batch(cfg_ref, B, seed=seed)
     cfg = ModelConfig.from_any(cfg_ref)
     W = frozen_from_oracle(ref, cfg, "cuda")
@@ -36,8 +37,13 @@ def build(cfg_ref, B, seed=1234):
     return ref, batch, cfg, eng
 
 
-def check_step(ref, batch, cfg, eng, tol_loss=1e-2, tol_pred=2e-2, tol_grad=6e-2, between=None):
+# per-stage bounds (relative Frobenius error of bf16 kernels vs the fp32 oracle). north_star: loss and readout <= 1e-2.
+STAGE_TOL = dict(frame_feats=2e-2, vis_tokens=3e-2, embeds=3e-2, hidden=3e-2, pooled=2e-2, hrf=2e-2, pred=1e-2, loss=1e-2)
+
+
+def check_step(ref, batch, cfg, eng, tol_grad=6e-2, between=None, stage_tol=None):
     """`between(ref, eng)` runs after the engine step and before the oracle step (e.g. to replay dropout masks)."""
+    tol = dict(STAGE_TOL, **(stage_tol or {}))
     loss3, pred = eng.loss_and_grads(to_dev(batch))
     torch.cuda.synchronize()
     loss3, pred = loss3.clone(), pred.clone()
@@ -45,11 +51,29 @@ def check_step(ref, batch, cfg, eng, tol_loss=1e-2, tol_pred=2e-2, tol_grad=6e-2
         between(ref, eng)
     out = ref.step(batch)
     out["loss"].backward()
-    B = batch["vision"].shape[0]
+    B, S, H = batch["vision"].shape[0], cfg.max_len, cfg.hidden
+    # ---- integer / layout stages: bit-exact
+    assert torch.equal(eng.weight_mask.cpu(), out["weight_mask"]), "HRF weight mask differs (litmodule.py:178-203)"
+    ids = out["input_ids"]
+    emb_gpu = eng.embeds.view(B, S, H).float().cpu()
+    for b in range(B):
+        s = int((ids[b] == -201).nonzero()[0])
+        assert int(eng.video_pos[b]) == s
+        text = torch.ones(S, dtype=torch.bool)
+        text[s:s + cfg.n_vis] = False
+        assert torch.equal(emb_gpu[b][text], out["embeds"][b][text].detach()), "text rows of the splice are exact table rows"
+    # ---- floating-point stages
     errs = {}
-    errs["weight_mask"] = float((eng.buf("hd_partial", (1,), torch.float32).new_zeros(1)).sum())  # placeholder 0
-    errs["vis_tokens"] = rel(eng.vis_tokens.view(B, cfg.n_vis, cfg.hidden), out["mm"])
-    errs["embeds"] = rel(eng.embeds.view(B, cfg.max_len, cfg.hidden), out["embeds"])
+    G2 = cfg.grid ** 2
+    errs["frame_feats"] = rel(eng.frame_feats.view(B, cfg.num_frames, G2, cfg.vit_hidden), out["frame_feats"])
+    errs["vis_tokens"] = rel(eng.vis_tokens.view(B, cfg.n_vis, H), out["mm"])
+    errs["embeds"] = rel(emb_gpu, out["embeds"])
+    hp = eng.hidden_pre_norm.float()
+    hn = hp * torch.rsqrt(hp.pow(2).mean(-1, keepdim=True) + cfg.rms_eps) * eng.W.llm["norm_w"].float()
+    # right-padded positions (ids == 0) are masked as KEYS in the reference (attention_mask) and carry HRF weight 0; being
+    # later in a causal sequence they cannot influence any valid row, and their own rows are never read -> compare valid rows
+    valid = torch.cat([torch.ones(B, S - ids.shape[1], dtype=torch.bool), ids.ne(0)], 1)
+    errs["hidden"] = rel(hn.view(B, S, H).cpu()[valid], out["hidden"][valid])
     errs["pooled"] = rel(eng.head_saved["pooled"], out["pooled"])
     errs["hrf"] = rel(eng.head_saved["hrf"], out["hrf"])
     errs["pred"] = rel(pred, out["pred"])
@@ -77,9 +101,8 @@ def check_step(ref, batch, cfg, eng, tol_loss=1e-2, tol_pred=2e-2, tol_grad=6e-2
     gerr = {k: rel(T.g(k), v) for k, v in g.items()}
     print("stage errors:", {k: "%.3g" % v for k, v in errs.items()})
     print("grad errors :", {k: "%.3g" % v for k, v in gerr.items()})
-    assert errs["vis_tokens"] < 3e-2 and errs["embeds"] < 3e-2
-    assert errs["loss"] < tol_loss, "loss %g vs %g" % (l_gpu, l_ref)
-    assert errs["pred"] < tol_pred
+    for k, v in errs.items():
+        assert v < tol[k], "stage %s: rel err %g >= %g (loss gpu %g oracle %g)" % (k, v, tol[k], l_gpu, l_ref)
     worst = max(gerr, key=gerr.get)
     assert gerr[worst] < tol_grad, "gradient %s rel err %g" % (worst, gerr[worst])
     return errs, gerr
@@ -112,6 +135,23 @@ def test_train_step_parity_tiny():
     from oracle.ref_model import tiny_config
     ref, batch, cfg, eng = build(tiny_config(), 2)
     check_step(ref, batch, cfg, eng)
+
+
+def test_train_step_parity_config1():
+    """BASELINE.json configs[0]: 2 ViT + 2 LLM layers at the full VideoLLaMA2-7B widths (1024/4096/14336, GQA 32:8), 8 frames
+    of 336^2 -> 845 visual tokens, S=2048, L_text=1204, 1000 parcels, LoRA B ~ N(0, 0.02) -- the production-shape paths of
+    vlb_weight_mask (169 tok/frame), vlb_splice_embed, vlb_conv3d_gather (T 8->5, 24->13), clip_embed / patch_im2col (577
+    tokens), hrf_pool (H=4096: all four row chunks, nch=64), se_pool/se_scale (C=4096), the pair GEMMs with the fused LoRA
+    k-block and SwiGLU epilogues, and 4:1 GQA attention inside a step, against the CPU fp32 oracle on identical weights.
+    (src/litmodule/videollama2_vlb_litmodule.py:229-306)"""
+    from oracle.ref_model import config1
+    ref, batch, cfg, eng = build(config1(), 2)
+    assert cfg.n_vis == 845 and cfg.l_text == 1204 and cfg.tok_per_frame == 169 and cfg.max_len == 2048
+    errs, gerr = check_step(ref, batch, cfg, eng)
+    # validation_step (litmodule.py:309-342) on the same batch: no dropout, same readout
+    loss3, pred = eng.eval_step(to_dev(batch))
+    out = ref.step(batch)
+    assert rel(pred, out["pred"]) < 1e-2 and abs(float(loss3[0]) - float(out["loss"])) / abs(float(out["loss"])) < 1e-2
 
 
 def test_train_step_parity_with_lora_dropout():
