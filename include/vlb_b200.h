@@ -108,6 +108,14 @@ int vlb_hrf_pool_fwd(const void* x, const void* norm_w, const void* ln1_w, const
 int vlb_hrf_pool_finalize(const void* partial_f32, const void* ln2_w, const void* ln2_b, void* pooled,
                           void* hrf, void* keep_scale_f32, int B, int H, int nch, float eps, float drop_p,
                           unsigned long long seed, void* stream);
+/* HRFConvolveLayer as a stand-alone layer (src/utils.py:40-56, exported by src/__init__.py:3-13):
+ * out_f32[b, e] = sum_s w_f32[b, s] * emb[b, s, e]  (emb bf16 [B, S, H], fp32 accumulate; out is zeroed inside).
+ * Backward of the same einsum: demb[b, s, :] = w[b, s] * dout[b, :] (bf16, nullable), dw_f32[b, s] = <emb[b, s, :], dout[b, :]>
+ * (nullable). Inside the training step the pooling is fused with the final RMSNorm and LN1 (vlb_hrf_pool_fwd). */
+int vlb_hrf_convolve_fwd(const void* emb, const void* w_f32, void* out_f32, int B, int S, int H, void* stream);
+int vlb_hrf_convolve_bwd(const void* emb, const void* w_f32, const void* dout_f32, void* demb, void* dw_f32,
+                         int B, int S, int H, void* stream);
+
 /* n = elements of this rank's [B, P_local] slice; n_total = B * P over all voxel shards (gradient scale 2/n_total). */
 int vlb_head_loss(const void* pred, const void* y_f32, void* dpred, void* acc_f32, long long n, long long n_total,
                   void* stream);

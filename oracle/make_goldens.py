@@ -294,6 +294,16 @@ def golden_lazyload():
     fake_h5py.reset()
 
 
+def golden_yaml():
+    """The datamodule / litmodule / trainer sections of the reference's two experiment YAMLs, as parsed (values only)."""
+    import yaml
+    for name in ("VLB_vllama2_friends_lora", "VLB_vllama2_friends_baseline"):
+        d = yaml.safe_load(open(os.path.join(REF, "config/experiment/%s.yaml" % name)))
+        with open(os.path.join(OUT, "%s.yaml" % name), "w") as f:
+            f.write("# datamodule / litmodule / trainer sections of the reference's config/experiment/%s.yaml as parsed by yaml.safe_load\n"
+                    "# (written by oracle/make_goldens.py; interpolations like ${subject} kept as strings)\n" % name)
+            yaml.safe_dump({k: d[k] for k in ("datamodule", "litmodule", "trainer")}, f, sort_keys=False)
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(1234)
@@ -330,6 +340,7 @@ def main():
     y = stc(x)
     sd = {k: v.detach().numpy() for k, v in stc.state_dict().items()}
     np.savez(os.path.join(OUT, "stc_connector.npz"), x=x.numpy(), y=y.detach().numpy(), **{"sd." + k: v for k, v in sd.items()})
+    golden_yaml()
     golden_video_chunks()
     golden_lazyload()
     golden_backbone()

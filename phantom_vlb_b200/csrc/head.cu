@@ -447,9 +447,82 @@ __global__ void head_gradnorm_kernel(const bf16* __restrict__ dpred, const bf16*
     if (threadIdx.x == 0) atomicAdd(sumsq, s);
 }
 
+// ---- HRFConvolveLayer on its own (src/utils.py:40-56): out[b, e] = sum_s w[b, s] * emb[b, s, e].
+// grid (col blocks, nch, B): a thread owns 8 adjacent columns and walks its slice of the token axis (rows with weight 0 are
+// skipped without being fetched); partial sums meet in the zeroed fp32 output through red.add.
+__global__ void __launch_bounds__(HT) hrf_convolve_fwd_kernel(const bf16* __restrict__ emb, const float* __restrict__ w,
+                                                              float* __restrict__ out, int S, int H, int rows_per) {
+    const int b = blockIdx.z, ch = blockIdx.y;
+    const int c = blockIdx.x * HT + threadIdx.x;
+    if (c * 8 >= H) return;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    const int s0 = ch * rows_per, s1 = min(S, s0 + rows_per);
+    for (int s = s0; s < s1; ++s) {
+        const float wgt = w[(size_t)b * S + s];
+        if (wgt == 0.f) continue;
+        float v[8]; load8(emb + ((size_t)b * S + s) * H + c * 8, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += wgt * v[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(out + (size_t)b * H + c * 8 + j, acc[j]);
+}
+
+// backward of the einsum, one CTA per token row: d_emb[b,s,:] = w[b,s] * g[b,:] (bf16), d_w[b,s] = <emb[b,s,:], g[b,:]>
+__global__ void __launch_bounds__(HT) hrf_convolve_bwd_kernel(const bf16* __restrict__ emb, const float* __restrict__ w,
+                                                              const float* __restrict__ g, bf16* __restrict__ demb,
+                                                              float* __restrict__ dw, int S, int H) {
+    __shared__ float red[32];
+    const size_t row = blockIdx.x;
+    const int b = (int)(row / S);
+    const float wgt = w[row];
+    float dot = 0.f;
+    for (int c = threadIdx.x; c * 8 < H; c += HT) {
+        float gv[8]; load8(g + (size_t)b * H + c * 8, gv);
+        if (dw) {
+            float v[8]; load8(emb + row * H + c * 8, v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dot += v[j] * gv[j];
+        }
+        if (demb) {
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = wgt * gv[j];
+            store8(demb + row * H + c * 8, o);
+        }
+    }
+    if (dw) {
+        dot = block_sum(dot, red);
+        if (threadIdx.x == 0) dw[row] = dot;
+    }
+}
+
 }  // namespace vlb
 
 using namespace vlb;
+
+extern "C" int vlb_hrf_convolve_fwd(const void* emb, const void* w_f32, void* out_f32, int B, int S, int H, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && B > 0 && S > 0, "hrf_convolve_fwd: B=%d S=%d H=%d", B, S, H);
+    cudaError_t e = cudaMemsetAsync(out_f32, 0, (size_t)B * H * sizeof(float), (cudaStream_t)stream);
+    VLB_REQUIRE(e == cudaSuccess, "hrf_convolve_fwd: memset failed (%s)", cudaGetErrorString(e));
+    const int colb = ceil_div(H / 8, HT);
+    int nch = ceil_div(num_sms() * 4, B * colb);
+    if (nch > S) nch = S;
+    if (nch < 1) nch = 1;
+    hrf_convolve_fwd_kernel<<<dim3(colb, nch, B), HT, 0, (cudaStream_t)stream>>>((const bf16*)emb, (const float*)w_f32,
+                                                                                (float*)out_f32, S, H, ceil_div(S, nch));
+    return check_launch("hrf_convolve_fwd");
+}
+
+extern "C" int vlb_hrf_convolve_bwd(const void* emb, const void* w_f32, const void* dout_f32, void* demb, void* dw_f32,
+                                    int B, int S, int H, void* stream) {
+    VLB_REQUIRE(H % 8 == 0 && B > 0 && S > 0 && (demb || dw_f32), "hrf_convolve_bwd: B=%d S=%d H=%d", B, S, H);
+    hrf_convolve_bwd_kernel<<<(unsigned)((size_t)B * S), HT, 0, (cudaStream_t)stream>>>(
+        (const bf16*)emb, (const float*)w_f32, (const float*)dout_f32, (bf16*)demb, (float*)dw_f32, S, H);
+    return check_launch("hrf_convolve_bwd");
+}
 
 extern "C" int vlb_hrf_pool_fwd(const void* x, const void* norm_w, const void* ln1_w, const void* ln1_b,
                                 const void* wmask_f32, void* partial_f32, int B, int S, int H, int nch, float eps_rms,

@@ -32,12 +32,14 @@ class Engine:
         # rank-r GEMM + masked add per projection input; p = 0 (benchmarks, parity) keeps the fully fused path.
         self.lora_dropout = float(lora_dropout or 0.0)
         self.drop_step = 0
+        self.seed_mix = 0           # set_seed(seed, rank): every data-parallel rank draws its own dropout masks
         self.drop_masks = None      # test hook: dict filled with uint8 keep masks keyed by (layer, site)
         self.saved = None
         # wide readouts (config 3, P ~ 250k): never materialise the rank-B ridge gradient; clip norm from Gram matrices and
         # AdamW in the epilogue of the gradient GEMM (vlb_head_gradnorm / vlb_head_adamw_fused)
         self.fused_head_opt = self.T.num_target_local * cfg.hidden >= (1 << 26)
         self.shard_reduce = None    # callable(tensor): in-place sum across voxel shards of the readout head (config 4)
+        self.row_gather = None      # callable(tensor) -> rows of all ranks (dp.gather_rows): replicated wide head under DP
         self.launches = 0
         self.profile = None
         self.fuse_swiglu = os.environ.get("VLB_FUSE_SWIGLU", "1") != "0"
@@ -185,8 +187,11 @@ class Engine:
             xa3=self.buf(t + "xa3", (M, 2 * r)), gu=self.buf(t + "gu", (M, 2 * I)), act=self.buf(t + "act", (M, I)),
             xa4=self.buf(t + "xa4", (M, r)))
 
+    def set_seed(self, seed=0, rank=0):
+        self.seed_mix = ((int(seed) & 0xFFFFFFFF) * 0x9E3779B1 + (int(rank) + 1) * 0x85EBCA77) & 0xFFFFFFFFFFFF
+
     def _drop_seed(self, l, site):
-        return 0xD0C0FFEE + (self.drop_step << 12) + l * 4 + site
+        return 0xD0C0FFEE + self.seed_mix + (self.drop_step << 12) + l * 4 + site
 
     def _lora_in(self, x, l, site, training):
         """Input of the LoRA A projection: x itself, or dropout(x) into a scratch buffer (regenerated in the backward)."""
@@ -332,15 +337,24 @@ class Engine:
         cfg = self.cfg
         vision = batch["vision"]
         B, Tn = vision.shape[0], vision.shape[1]
-        assert Tn == cfg.num_frames and vision.dtype in (torch.float32, torch.uint8)     # uint8: raw frames (f-1)
+        assert vision.dtype in (torch.float32, torch.uint8)                               # uint8: raw frames (f-1)
+        if Tn != cfg.num_frames:
+            # the frame count is a property of the data (window * frames_per_tr, extractfeatures.py:198-212): the reference
+            # passes whatever T the datamodule holds, so the engine follows the batch (buffers are keyed by shape)
+            cfg.num_frames = Tn
         assert batch["language"].shape[1] == cfg.l_text, "text length must be max_len - n_vis + 1 (litmodule.py:180-181)"
         feats = self.vit_forward(vision.reshape(B * Tn, 3, cfg.image_size, cfg.image_size))
         vis = self.stc_forward(feats, B)
-        ids = ops.ids_to_long(batch["language"].contiguous())
+        lang = batch["language"].contiguous()
+        ids = lang if lang.dtype == torch.int64 else ops.ids_to_long(lang)
         x0 = self.buf("L0_x", (B * cfg.max_len, cfg.hidden))
         _, self.video_pos = ops.splice_embed(ids, self.W.llm["embed"], vis, cfg.n_vis, out=x0)
-        wm = ops.weight_mask(batch["padvals"].contiguous(), batch["vis_weights"].contiguous(),
-                             batch["lang_weights"].contiguous(), cfg.tok_per_frame, cfg.max_len)
+        if batch.get("weight_mask") is not None:          # forward(x_video, x_lang, weight_mask): caller-built row
+            wm = batch["weight_mask"].to(torch.float32).contiguous()
+            assert wm.shape == (B, cfg.max_len)
+        else:
+            wm = ops.weight_mask(batch["padvals"].contiguous(), batch["vis_weights"].contiguous(),
+                                 batch["lang_weights"].contiguous(), cfg.tok_per_frame, cfg.max_len)
         self.launches += 4
         self.vis_tokens, self.embeds, self.frame_feats, self.weight_mask = vis, x0, feats, wm
         hidden = self.decoder_forward(x0, B, save=save)
@@ -378,7 +392,7 @@ class Engine:
         keep = self.buf("hd_keep", (B, H), torch.float32) if drop > 0 else None
         self.rng_step = getattr(self, "rng_step", 0) + 1
         _l.call("vlb_hrf_pool_finalize", _l.ptr(partial), _l.ptr(T.w("ln2_w")), _l.ptr(T.w("ln2_b")), _l.ptr(pooled),
-                _l.ptr(hrf), _l.ptr(keep), B, H, nch, cfg.head_ln_eps, float(drop), 0x5EED0000 + self.rng_step, _l.cur_stream())
+                _l.ptr(hrf), _l.ptr(keep), B, H, nch, cfg.head_ln_eps, float(drop), 0x5EED0000 + self.seed_mix + self.rng_step, _l.cur_stream())
         pred = self.gemm(hrf, T.w("ridge_w"), self.buf("hd_pred", (B, P)), bias=T.w("ridge_b"))
         acc = self.buf("hd_acc", (2,), torch.float32)
         acc.zero_()
@@ -503,18 +517,37 @@ class Engine:
                        allreduce=None):
         """clip_grad_norm_(max_norm) + AdamW on the flat buffer; `allreduce(tensor)` sums gradients across ranks first."""
         T = self.T
+        fused = self.fused_head_opt
+        off_w, shape_w = T.offsets["ridge_w"]
+        n_w = math.prod(shape_w)
+        end_w = off_w + (n_w + 7) // 8 * 8
+        dp_rows = None
         if allreduce is not None:
-            allreduce(T.grad)
+            if fused and self.shard_reduce is None:
+                # replicated wide head under data parallel: its rank-B gradient is never materialised, so there is nothing to
+                # all-reduce for it -- the ranks exchange the B rows of dpred / hrf / pred instead (sum over ranks of
+                # dpred_r^T hrf_r == gathered^T gathered) and every rank forms the same global gradient tile by tile
+                if self.row_gather is None:
+                    raise RuntimeError("fused wide-head optimiser with a replicated head under data parallel needs "
+                                       "engine.row_gather (dp.gather_rows); refusing to step with rank-local gradients")
+                hs = self.head_saved
+                dp_rows = tuple(self.row_gather(hs[k]) for k in ("dpred", "hrf", "pred"))
+                allreduce(T.grad[:off_w])
+                allreduce(T.grad[end_w:])
+            else:
+                allreduce(T.grad)
         T.step_count += 1
         hyper = (float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), T.step_count, float(max_norm),
                  1.0 / world_size)
         st = _l.cur_stream()
         T.sumsq.zero_()
-        fused = self.fused_head_opt
-        off_w, shape_w = T.offsets["ridge_w"]
-        n_w = math.prod(shape_w)
-        end_w = off_w + (n_w + 7) // 8 * 8
         gp = T.grad.data_ptr()
+        if fused:
+            hs = self.head_saved
+            h_dpred, h_hrf, h_pred = dp_rows if dp_rows is not None else (hs["dpred"], hs["hrf"], hs["pred"])
+            # gradients are kept as SUMS over ranks and scaled by 1/world inside the kernels; the ridge term 2*lambda*W each
+            # rank would have contributed is therefore counted world times
+            lam = self.cfg.l2_lambda * (world_size if dp_rows is not None else 1)
 
         def sumsq(lo, hi):                      # squared norm of the materialised gradients in [lo, hi), ridge_w skipped if fused
             for a, b in (((lo, min(hi, off_w)), (max(lo, end_w), hi)) if fused else ((lo, hi),)):
@@ -525,21 +558,20 @@ class Engine:
         split = T.offsets["ln1_w"][0] if self.shard_reduce is not None else T.numel
         sumsq(0, split)
         if fused:                               # ||dW_ridge||^2 from Gram matrices: the 4 GB gradient is never formed
-            hs, cfg = self.head_saved, self.cfg
-            N = hs["dpred"].shape[0]
+            N = h_dpred.shape[0]
             N8 = (N + 7) // 8 * 8               # GEMM output columns come in multiples of 8: zero-padded sample rows
-            dp, hr = hs["dpred"], hs["hrf"]
+            dp, hr = h_dpred, h_hrf
             if N8 != N:
                 dp = self.buf("hd_dpred_pad", (N8, dp.shape[1])); hr = self.buf("hd_hrf_pad", (N8, hr.shape[1]))
                 dp.zero_(); hr.zero_()
-                dp[:N].copy_(hs["dpred"]); hr[:N].copy_(hs["hrf"])
+                dp[:N].copy_(h_dpred); hr[:N].copy_(h_hrf)
             gd = self.buf("hd_gram_d", (N8, N8), torch.float32); gh = self.buf("hd_gram_h", (N8, N8), torch.float32)
             gd.zero_(); gh.zero_()
             self.gemm(dp, dp, gd, out_f32=True, accumulate=True)
             self.gemm(hr, hr, gh, out_f32=True, accumulate=True)
-            _l.call("vlb_head_gradnorm", _l.ptr(hs["dpred"]), _l.ptr(hs["pred"]), _l.ptr(T.w("ridge_b")), _l.ptr(gd), _l.ptr(gh),
+            _l.call("vlb_head_gradnorm", _l.ptr(h_dpred), _l.ptr(h_pred), _l.ptr(T.w("ridge_b")), _l.ptr(gd), _l.ptr(gh),
                     N8, _l.ptr(self.buf("hd_wsq_local", (1,), torch.float32)), _l.ptr(T.sumsq), N, T.num_target_local,
-                    cfg.l2_lambda, st)
+                    lam, st)
             self.launches += 1
         if self.shard_reduce is not None:
             # voxel-sharded head: ridge W/b gradients are rank-private (sum their squares across ranks), the LN1/LN2
@@ -554,12 +586,11 @@ class Engine:
                 self.launches += 1
 
         if fused:
-            hs, cfg = self.head_saved, self.cfg
             adamw(0, off_w)
-            _l.call("vlb_head_adamw_fused", _l.ptr(hs["dpred"]), hs["dpred"].stride(0), _l.ptr(hs["hrf"]), hs["hrf"].stride(0),
-                    hs["dpred"].shape[0], T.num_target_local, cfg.hidden, T.param.data_ptr() + 4 * off_w,
+            _l.call("vlb_head_adamw_fused", _l.ptr(h_dpred), h_dpred.stride(0), _l.ptr(h_hrf), h_hrf.stride(0),
+                    h_dpred.shape[0], T.num_target_local, self.cfg.hidden, T.param.data_ptr() + 4 * off_w,
                     T.m.data_ptr() + 4 * off_w, T.v.data_ptr() + 4 * off_w, T.param_bf16.data_ptr() + 2 * off_w,
-                    _l.ptr(T.sumsq), *hyper, cfg.l2_lambda, st)
+                    _l.ptr(T.sumsq), *hyper, lam, st)
             self.launches += 1
             adamw(end_w, T.numel)
         else:

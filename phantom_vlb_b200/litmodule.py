@@ -11,9 +11,12 @@ and argument meaning, with the arithmetic replaced by the libvlb_b200 engine.
 Trainable state is ONE nn.Parameter (`flat`, fp32) aliasing the engine's flat master buffer, so Lightning's DDP,
 gradient clipping and checkpointing all operate on a single contiguous tensor; `named_trainables()` exposes the
 PEFT-style views for checkpoint interchange.
-`model_path` accepts "random:7b" | "random:config1" | "random:tiny" (random-init backbones for parity runs and
-benchmarks, there is no network for checkpoints here) or a prepared FrozenWeights object via `frozen=`.
+`model_path` is a LOCAL checkpoint directory (config.json + *.safetensors / pytorch_model*.bin with the Hugging Face /
+VideoLLaMA2 key names -- weights.py; the reference itself loads with local_files_only=True, litmodule.py:81), or
+"random:7b" | "random:config1" | "random:tiny" (random-init backbones of the exact architecture for parity runs and
+benchmarks), or a prepared FrozenWeights object passed as configure_model(frozen=...).
 """
+import os
 from dataclasses import dataclass
 
 import torch
@@ -74,8 +77,9 @@ def model_config_for(config: VLBLitModuleConfig, num_frames=8) -> ModelConfig:
         common["num_frames"] = 4
         return ModelConfig(vit_hidden=128, vit_layers=3, vit_heads=2, vit_mlp=256, image_size=56, hidden=256, layers=2,
                            heads=2, kv_heads=1, mlp=512, vocab=512, stc_depth=2, max_len=128, lang_w_len=16, **common)
-    raise NotImplementedError("model_path=%r: loading a Hugging Face checkpoint is not wired yet; use random:7b / "
-                              "random:config1 / random:tiny or pass frozen= to configure_model" % (config.model_path,))
+    raise FileNotFoundError("model_path=%r is neither a local checkpoint directory nor random:7b / random:config1 / "
+                            "random:tiny (hub ids cannot be resolved: the reference loads with local_files_only=True, "
+                            "litmodule.py:81)" % (config.model_path,))
 
 
 class _StepFn(torch.autograd.Function):
@@ -103,16 +107,39 @@ class FusedClipAdamW(torch.optim.Optimizer):
 
     @torch.no_grad()
     def step(self, closure=None):
-        loss = closure() if closure is not None else None
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():                   # torch.optim convention: the closure re-evaluates the model
+                loss = closure()
         grp = self.param_groups[0]
         p = grp["params"][0]
         T = self.engine.T
+        if torch.distributed.is_available() and torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1 \
+                and self.engine.fused_head_opt and self.engine.shard_reduce is None and self.allreduce is None:
+            raise RuntimeError("wide replicated readout head under DDP: its rank-B gradient is not part of flat.grad; shard the "
+                               "head by voxel (target_slice + engine.shard_reduce) or set optimizer.allreduce + "
+                               "engine.row_gather")
         if p.grad is not None and p.grad.data_ptr() != T.grad.data_ptr():
             T.grad.copy_(p.grad)
         self.engine.optimizer_step(grp["lr"], betas=grp["betas"], eps=grp["eps"], weight_decay=grp["weight_decay"],
                                    max_norm=self.max_norm, world_size=self.world_size if self.allreduce else 1,
                                    allreduce=self.allreduce)                 # under DDP p.grad is already averaged
         return loss
+
+    # Adam moments and the step count live in the engine's flat buffers: expose them the torch.optim way, so Lightning's
+    # checkpoint["optimizer_states"] carries them and trainer.fit(ckpt_path=...) resumes bias correction and moments
+    def state_dict(self):
+        T = self.engine.T
+        sd = super().state_dict()
+        sd["vlb"] = {"adam_m": T.m.detach().cpu(), "adam_v": T.v.detach().cpu(), "step_count": int(T.step_count)}
+        return sd
+
+    def load_state_dict(self, state_dict):
+        vlb = state_dict.get("vlb")
+        super().load_state_dict({k: v for k, v in state_dict.items() if k != "vlb"})
+        if vlb is not None:
+            T = self.engine.T
+            T.m.copy_(vlb["adam_m"]); T.v.copy_(vlb["adam_v"]); T.step_count = int(vlb["step_count"])
 
 
 class VLBLitModule(LightningModule):
@@ -131,9 +158,17 @@ class VLBLitModule(LightningModule):
         if self.config.use_lora == self.config.freeze_backbone:
             raise NotImplementedError("full fine-tuning (use_lora=False, freeze_backbone=False) is not built, and "
                                       "use_lora=True with freeze_backbone=True is contradictory (litmodule.py:86-120)")
-        mc = model_config or model_config_for(self.config)
         dev = torch.device(device)
-        W = frozen if frozen is not None else frozen_random(mc, dev, seed)
+        path = str(self.config.model_path)
+        if frozen is None and model_config is None and os.path.isdir(path):
+            # load_pretrained_vllama2 (litmodule.py:58-122): config.json + weight files of a local VideoLLaMA2 checkpoint
+            from .weights import load_pretrained
+            mc, W = load_pretrained(path, dev, num_target=self.config.num_target, l2_lambda=self.config.l2_lambda,
+                                    lora_r=self.config.lora_r or 16, lora_alpha=self.config.lora_alpha or 32,
+                                    use_lora=bool(self.config.use_lora))
+        else:
+            mc = model_config or model_config_for(self.config)
+            W = frozen if frozen is not None else frozen_random(mc, dev, seed)
         T = Trainables(mc, dev, target_slice=target_slice)
         T.init_default(seed, lora_b_std=lora_b_std)
         self.engine = Engine(mc, W, T, device=dev, dropout_rate=self.config.dropout_rate,
@@ -141,8 +176,11 @@ class VLBLitModule(LightningModule):
         self.model_config = mc
         self.flat = torch.nn.Parameter(T.param)           # aliases the fp32 master buffer
         self.hrf_layer = HRFConvolveLayer()
-        self.ridge_layer = RidgeRegressionLayer(mc.hidden, T.num_target_local, self.config.l2_lambda)
-        self._params_dirty = False
+        self.ridge_layer = RidgeRegressionLayer(mc.hidden, T.num_target_local, self.config.l2_lambda, own_parameters=False)
+        self.ridge_layer.bind(lambda: T.w("ridge_w"), lambda: T.w("ridge_b"))    # the readout slice of the flat buffer
+        self._seen_version = self.flat._version
+        rank = torch.distributed.get_rank() if torch.distributed.is_available() and torch.distributed.is_initialized() else 0
+        self.engine.set_seed(seed, rank)
 
     def named_trainables(self):
         """PEFT-style (name, fp32 view) pairs of the flat buffer, B matrices still transposed ([r, N])."""
@@ -200,8 +238,43 @@ class VLBLitModule(LightningModule):
             T = self.engine.T
             T.m.copy_(ck["adam_m"]); T.v.copy_(ck["adam_v"]); T.step_count = int(ck["step_count"])
 
+    # nn.Module protocol: the module's state IS the adapter + head tensors under the reference's key names, so Lightning's
+    # save_checkpoint / load_from_checkpoint / fit(ckpt_path=...) round-trip without knowing about the flat buffer
+    def state_dict(self, *args, destination=None, prefix="", keep_vars=False):
+        if self.engine is None:
+            return super().state_dict(*args, destination=destination, prefix=prefix, keep_vars=keep_vars)
+        out = destination if destination is not None else {}
+        for k, v in self.adapter_state_dict().items():
+            out[prefix + k] = v
+        return out
+
+    def load_state_dict(self, state_dict, strict=True, assign=False):
+        if self.engine is None:
+            raise RuntimeError("call configure_model() before load_state_dict (Lightning does: configure_model hook)")
+        if "flat" in state_dict:                        # a raw dump of the flat master
+            self.engine.T.param.copy_(state_dict["flat"].to(self.engine.T.param.device))
+            self.engine.T.sync_working()
+            missing = []
+        else:
+            missing = self.load_adapter_state_dict(state_dict, strict=strict)
+        known = {k for k, _, _ in self._adapter_views()} | {"flat"}
+        unexpected = [k for k in state_dict if k not in known]
+        if strict and unexpected:
+            raise KeyError("unexpected keys in checkpoint, e.g. %s" % unexpected[0])
+        self._seen_version = self.flat._version
+        return torch.nn.modules.module._IncompatibleKeys(missing, unexpected)
+
     def on_save_checkpoint(self, checkpoint):           # Lightning hook: trainer.save_checkpoint(...) (train.py:58)
         checkpoint["state_dict"] = self.adapter_state_dict()
+        T = self.engine.T                               # also kept here for checkpoints written without optimizer_states
+        checkpoint["vlb_optimizer"] = {"adam_m": T.m.detach().cpu(), "adam_v": T.v.detach().cpu(), "step_count": int(T.step_count)}
+
+    def on_load_checkpoint(self, checkpoint):           # Lightning hook, runs before load_state_dict
+        self.configure_model()
+        vo = checkpoint.get("vlb_optimizer")
+        if vo is not None:
+            T = self.engine.T
+            T.m.copy_(vo["adam_m"]); T.v.copy_(vo["adam_v"]); T.step_count = int(vo["step_count"])
 
     # ------------------------------------------------------------------ helpers
     def make_weight_mask(self, pad_vals, vis_weights, lang_weights, lang_len, max_len):
@@ -217,18 +290,34 @@ class VLBLitModule(LightningModule):
         return {k: (v if v.device == dev else v.to(dev, non_blocking=True)) for k, v in batch.items()}
 
     def _refresh(self):
-        # an external optimiser (plain torch AdamW) may have written `flat`; FusedClipAdamW keeps copies in sync itself
-        if self._params_dirty:
+        # anything other than FusedClipAdamW that wrote `flat` in place (a plain torch optimiser, a manual copy_) bumps the
+        # tensor's version counter: refresh the bf16 working copy and the staged LoRA B matrices the kernels read
+        if self.flat._version != self._seen_version:
             self.engine.T.sync_working()
-            self._params_dirty = False
+            self._seen_version = self.flat._version
 
     # ------------------------------------------------------------------ forward / steps
-    def forward(self, x_video, x_lang, weight_mask=None, attention_mask=None, batch=None):
-        """Reference signature (litmodule.py:229). The weight mask and attention mask are recomputed on the device
-        from `batch`; returns (regression_output, l2_reg)."""
-        assert batch is not None, "pass the datamodule batch dict (batch=...)"
-        out, pred = self.engine.eval_step(self._to_device(batch))
-        return pred, out[2]
+    def forward(self, x_video, x_lang, weight_mask, attention_mask=None):
+        """Reference signature and argument meaning (litmodule.py:229-256): x_video = [(Tensor[T,3,H,W], "video")] * B (or a
+        stacked [B,T,3,H,W] tensor), x_lang = token ids [B, L_text] incl. the <video> id, weight_mask = HRF weight row
+        [B, max_len] (make_weight_mask), attention_mask = x_lang.ne(0). Returns (regression_output [B,P], l2_reg).
+        The attention mask carries no extra information here: padding is on the right, so under the causal mask no valid
+        position can see a padded one, and padded positions have HRF weight 0. Inference only (dropout follows
+        self.training); gradients flow through training_step."""
+        self._refresh()
+        dev = self.engine.dev
+        if isinstance(x_video, (list, tuple)):
+            x_video = torch.stack([v[0] if isinstance(v, (list, tuple)) else v for v in x_video], 0)
+        vision = x_video.to(dev)
+        if vision.dtype != torch.uint8:
+            vision = vision.float()
+        batch = {"vision": vision.contiguous(), "language": x_lang.to(dev).long(), "weight_mask": weight_mask.to(dev)}
+        B = vision.shape[0]
+        with torch.no_grad():
+            hidden, wm = self.engine.backbone_forward(batch, save=False)
+            y0 = self.engine.buf("fw_zero_targets", (B, self.engine.T.num_target_local), torch.float32)
+            out, pred = self.engine.head_forward(hidden, wm, y0, B, training=self.training)
+        return pred.clone(), out[2].clone()
 
     def training_step(self, batch):
         self._refresh()

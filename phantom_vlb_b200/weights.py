@@ -205,5 +205,8 @@ def load_frozen(src, cfg: ModelConfig, dev, parts=("vit", "stc", "llm")):
 def load_pretrained(path, dev, **overrides):
     """model_path=<local dir> -> (ModelConfig, FrozenWeights)."""
     src, hf = open_checkpoint(path)
+    depth = len({k.split(".")[3] for k in src.keys() if k.startswith(PJ + "s1.b")})      # RegStage depth: blocks b1..bN
+    if depth:
+        overrides.setdefault("stc_depth", depth)
     cfg = model_config_from_hf(hf, **overrides)
     return cfg, load_frozen(src, cfg, dev)

@@ -13,7 +13,7 @@ import torch
 
 from oracle import indexing
 from phantom_vlb_b200 import utils
-from phantom_vlb_b200.datamodule import (SyntheticVLBDataset, VLBDataModule, VLBDataModuleConfig, split_files)
+from phantom_vlb_b200.datamodule import (SyntheticVLBDataset, VLBDataModule, VLBDataModuleConfig, season_files, split_train_val)
 from phantom_vlb_b200.litmodule import VLBLitModule, VLBLitModuleConfig, model_config_for
 
 LIT_KEYS = ["model_path", "freeze_backbone", "use_lora", "lora_r", "lora_alpha", "lora_dropout", "dropout_rate", "num_target",
@@ -61,7 +61,7 @@ def test_datamodule_config_keys_and_defaults():
     assert [f.name for f in fields] == DATA_KEYS
     d = {f.name: f.default for f in fields}
     assert d["batch_size"] == 1 and d["num_workers"] == 0                    # datamodule.py:40-41
-    for name in ("train_dataloader", "val_dataloader", "x_dataloader"):
+    for name in ("train_dataloader", "val_dataloader"):
         assert callable(getattr(VLBDataModule, name))
 
 
@@ -72,11 +72,13 @@ def test_file_split_draws_one_validation_file(tmp_path):
             (tmp_path / f"sub-01_{s}_chunk{k}.h5").write_bytes(b"")
     cfg = VLBDataModuleConfig(lazyload_path=str(tmp_path / "sub-01_s*_chunk*.h5"), subject="sub-01", seasons=["s1", "s2"],
                               delay=3, window=3, random_state=1234, shuffle_val_data=False)
-    train, val = split_files(cfg)
+    files = season_files(cfg)
+    assert files == sorted(str(p) for p in tmp_path.iterdir())                # per season, sorted
+    train, val = split_train_val(files, cfg.random_state)
     assert len(val) == 1 and len(train) == 5 and val[0] not in train
-    files = sorted(str(p) for p in tmp_path.iterdir())
-    assert val == np.random.RandomState(1234).choice(files, 1).tolist()
-    assert split_files(cfg) == (train, val)                                   # deterministic
+    for seed in (0, 1, 7, 1234, 99999):                                       # the SAME held-out file the reference draws
+        assert split_train_val(files, seed)[1] == np.random.RandomState(seed).choice(files, 1).tolist()
+    assert split_train_val(files, cfg.random_state) == (train, val)           # deterministic
     assert os.path.basename(val[0]).startswith("sub-01_")
 
 

@@ -50,4 +50,4 @@ def test_vectorised_hrf_weights_match_scalar():
     w = hrf_weights(lags)
     assert w.dtype == np.float64 and w.shape == lags.shape
     assert np.allclose(w, [get_hrf_weight(float(t)) for t in lags], rtol=1e-12, atol=0)
-    assert w[-4] == 0.0 and w[-3] == 0.0 and abs(hrf_weights([5.0])[0] - 1.0) < 0.05             # peak-normalised near 5 s
+    assert w[-4] == 0.0 and w[-3] == 0.0 and 0.25 < hrf_weights([5.0])[0] < 0.3          # nilearn regressor: unit-sum HRF x 1 s event
