@@ -130,6 +130,30 @@ int vlb_hrf_pool_bwd(const void* x, const void* norm_w, const void* ln1_w, const
                      const void* dpooled_f32, void* dx, void* dg1_f32, void* db1_f32, int B, int S, int H,
                      int nch, float eps_rms, float eps_ln, void* stream);
 
+/* ------------------------------------------------------------------ LoRA input dropout on the fused path
+ * peft lora.Linear computes y = W x + s B(A(dropout(x))) with one independent Bernoulli mask per adapter (reference
+ * lora_dropout 0.1, config/experiment/VLB_vllama2_friends_lora.yaml:30; src/litmodule/videollama2_vlb_litmodule.py:113-120).
+ * vlb_dropout_bits draws the keep mask of one adapter over its input [n_tok, n_feat] as packed bits, exact p (32-bit uniform
+ * against p * 2^32): word64[fb * n_tok + tok] holds features [64 fb, 64 fb + 64) of token tok. The masks are consumed where the
+ * masked value is needed, never materialised as activations:
+ *   vlb_lora_down_masked     xa[n_tok, 16 n] = alpha * (keep_a . x) A_a^T for the n <= 3 adapters sharing the input x
+ *                            (A [16 n, n_feat] stacked lora_A matrices); x is streamed once.
+ *   vlb_lora_grad_a_masked   dA_f32[16 n, n_feat] += alpha * t_a^T (keep_a . x), t [n_tok, 16 n] = s dy B.
+ *   vlb_gemm_dx_lora_masked  out[M, N] = dy[M, K] W[K, N] + scale * sum_a keep_a . (t_a A_a)   (W = forward weight
+ *                            [out = K, in = N]; the adapter branch of dX is formed in the GEMM epilogue).
+ *   vlb_gemm_down_dx_swiglu_bwd_masked   the same for the down projection with the SwiGLU backward in the epilogue. */
+int vlb_dropout_bits(void* bits64, long long n_tok, int n_feat, float p, unsigned long long seed, void* stream);
+int vlb_lora_down_masked(const void* x, int ldx, const void* A, int lda, void* xa, int ldxa, int n_tok, int n_feat,
+                         int n_adapters, const void* bits0, const void* bits1, const void* bits2, float alpha, void* stream);
+int vlb_lora_grad_a_masked(const void* x, int ldx, const void* t, int ldt, void* dA_f32, int ldda, int n_tok, int n_feat,
+                           int n_adapters, const void* bits0, const void* bits1, const void* bits2, float alpha, void* stream);
+int vlb_gemm_dx_lora_masked(const void* dy, int lddy, const void* W, int ldw, void* out, int ldo, int M, int N, int K,
+                            const void* t, int ldt, const void* A, int lda, int n_adapters, const void* bits0,
+                            const void* bits1, const void* bits2, float scale, void* stream);
+int vlb_gemm_down_dx_swiglu_bwd_masked(const void* dy, int lddy, const void* wd, int ldw, const void* gu, int ldgu,
+                                       void* dgu, int lddgu, int M, int I, int H, const void* t, int ldt, const void* A,
+                                       int lda, const void* bits, float scale, void* stream);
+
 /* ------------------------------------------------------------------ LoRA input dropout (peft lora.Linear: B(A(dropout(x))),
  * reference lora_dropout 0.1, config/experiment/VLB_vllama2_friends_lora.yaml:30). Counter-based mask from (seed, element
  * index), probability quantised to 1/256; vlb_dropout_add applies the same mask to the adapter branch of dX. mask_u8 may be

@@ -33,9 +33,31 @@ constexpr int G2_TMEM_COLS = 512;
 // The plain variant (SWIGLU == 0) runs EIGHT epilogue warps (384 threads): two warpgroups, each owning 128 of the tile's 256
 // columns with its own staging buffer, named barrier and TMA-store issuer. With four warps the K = 1024 ViT GEMMs whose
 // epilogue carries an activation or a residual were epilogue-bound (fc1 650, o-proj 500 TF/s against 1350 plain).
-template <int SWIGLU> __host__ __device__ constexpr int g2_threads() { return SWIGLU == 0 ? 384 : 256; }
-template <bool B_MN, int SWIGLU = 0>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2_threads<SWIGLU>(), 1)
+template <int SWIGLU, bool LORA = false> __host__ __device__ constexpr int g2_threads() { return (SWIGLU == 0 || (SWIGLU == 2 && LORA)) ? 384 : 256; }
+
+// LORA_EPI (dX GEMMs under LoRA dropout): the adapter branch of the input gradient, 1/(1-p) * keep_a . (t_a A_a), cannot ride in
+// the accumulator as a k-block (the keep mask sits between the rank-16 product and the sum), so the epilogue forms it on the
+// CUDA cores: A_a's 256 columns of the tile are staged in the ring stage this mode leaves unused (5-deep ring), every thread
+// holds its row of t in registers, and per 8 columns 16 broadcast LDS.128 + 128 FMA per adapter run in the shadow of the next
+// tile's main loop. v[i] += scale * keep_i * sum_j t[j] A[j][col + i]
+__device__ __forceinline__ void lora_rank16_add8(float (&v)[8], const float* t, uint32_t a_col, int row_bytes,
+                                                 unsigned int byte, float scale) {
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        float f[8];
+        unpack8(lds128(a_col + j * row_bytes), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(t[j], f[i], acc[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] += ((byte >> i) & 1u) ? acc[i] * scale : 0.f;
+}
+
+template <bool B_MN, int SWIGLU = 0, bool LORA = false>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2_threads<SWIGLU, LORA>(), 1)
 gemm2_tcgen05_kernel(const GemmParams p,
                      const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
@@ -66,7 +88,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 2 * (g2_threads<SWIGLU>() - 128)); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 2 * (g2_threads<SWIGLU, LORA>() - 128)); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc_2sm<G2_TMEM_COLS>(tmem_ptr);
@@ -157,10 +179,105 @@ gemm2_tcgen05_kernel(const GemmParams p,
                     }
                 }
             }
-            mbar_wait(&tfull_bar[as], aphase);
-            tc_fence_after();
             const int m = m0 + row;
             const bool m_ok = m < p.M;
+            float lt[LORA ? 48 : 1];                        // this row of t (rank-16 coefficients of up to three adapters)
+            uint32_t la = 0;                                // this warpgroup's staged columns of A (shared-space address)
+            constexpr int LA_ROW_BYTES = (G2_BN / 2) * 2;  // each warpgroup stages the 128 columns it owns
+            if constexpr (LORA) {
+                // every thread of the warpgroup is past the last bar.sync of its previous tile, so nobody still reads the old A.
+                // plain variant: ring stage 5 is free (5-deep ring); SwiGLU variant: stages 4 and 5 are free (4-deep ring), the A
+                // slots of those hold the second warpgroup's output staging buffers, the B slot of stage 4 the two A regions
+                uint8_t* law = SWIGLU == 2 ? smem_b + (STAGES - 2) * G2_B_BYTES + wg * (G2_B_BYTES / 2)
+                                           : (wg == 0 ? smem_a : smem_b) + (STAGES - 1) * G2_A_BYTES;
+                constexpr int CHUNKS_PER_ROW = LA_ROW_BYTES / 16;
+                const int tid = q * 32 + lane;
+                const int ncol0 = n0 + wg * (G2_BN / 2);
+                for (int idx = tid; idx < 16 * p.lr_na * CHUNKS_PER_ROW; idx += 128) {
+                    const int rj = idx / CHUNKS_PER_ROW, c16 = idx - rj * CHUNKS_PER_ROW;
+                    const int ncol = ncol0 + c16 * 8;
+                    uint4 val = make_uint4(0u, 0u, 0u, 0u);
+                    if (ncol < p.N) val = __ldg(reinterpret_cast<const uint4*>(p.lr_A + (size_t)rj * p.lr_lda + ncol));
+                    sts128(smem_u32(law) + rj * LA_ROW_BYTES + c16 * 16, val);
+                }
+                la = smem_u32(law);
+#pragma unroll
+                for (int c = 0; c < 6; ++c) {
+                    uint4 tv = make_uint4(0u, 0u, 0u, 0u);
+                    if (m_ok && c * 8 < 16 * p.lr_na) tv = __ldg(reinterpret_cast<const uint4*>(p.lr_t + (size_t)m * p.lr_ldt + c * 8));
+                    float f[8]; unpack8(tv, f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) lt[c * 8 + j] = f[j];
+                }
+            }
+            mbar_wait(&tfull_bar[as], aphase);
+            tc_fence_after();
+            if constexpr (SWIGLU == 2 && LORA) {
+                // Two warpgroups (384 threads), each owning 128 of the tile's 256 columns with its own pair of staging buffers:
+                // with four warps the adapter term (16 LDS.128 + 128 FMA per 8 columns) on top of the SwiGLU backward made the
+                // epilogue longer than the K = 4096 main loop. Rolled over 8-column chunks: unrolled, this code overflowed the
+                // instruction cache and the warps stalled on instruction fetch.
+                uint8_t* cdg = wg == 0 ? smem_cd : smem_a + (STAGES - 2) * G2_A_BYTES;
+                uint8_t* cdu = cdg + CD_STAGE_BYTES;
+                const int I = p.swiglu_I;
+                const bf16* gurow = p.sw_gu + (size_t)(m_ok ? m : 0) * p.sw_ld;
+                const int s_first = wg * (G2_BN / 128);
+                uint4 gvn = __ldg(reinterpret_cast<const uint4*>(gurow + n0 + s_first * 64));
+                uint4 uvn = __ldg(reinterpret_cast<const uint4*>(gurow + I + n0 + s_first * 64));
+                unsigned long long kwn = ~0ull;
+                if (m_ok) kwn = __ldg(p.lr_bits[0] + (size_t)((n0 >> 6) + s_first) * p.M + m);
+#pragma unroll 1
+                for (int sl = 0; sl < G2_BN / 128; ++sl) {
+                    const int s = s_first + sl;
+                    const unsigned long long kw = kwn;
+                    if (m_ok && sl + 1 < G2_BN / 128) kwn = __ldg(p.lr_bits[0] + (size_t)((n0 >> 6) + s + 1) * p.M + m);
+                    if (issuer) tma_store_wait_read<0>();
+                    asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
+#pragma unroll 1
+                    for (int ch = 0; ch < 8; ++ch) {
+                        const int c0 = s * 64 + ch * 8;
+                        const uint4 gv = gvn, uv = uvn;
+                        {   // gate / up of the NEXT chunk: the global round trip overlaps this chunk's math
+                            const int cn = s_first * 64 + ((sl * 64 + ch * 8 + 8) & (G2_BN / 2 - 1));
+                            gvn = __ldg(reinterpret_cast<const uint4*>(gurow + n0 + cn));
+                            uvn = __ldg(reinterpret_cast<const uint4*>(gurow + I + n0 + cn));
+                        }
+                        uint32_t r8[8];
+                        tmem_ld8(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + c0), r8);
+                        tmem_ld_wait();
+                        float g[8], u[8], dg[8], du[8], dv[8];
+                        unpack8(gv, g); unpack8(uv, u);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r8[j]) * p.alpha;
+                        lora_rank16_add8(dv, lt, la + (sl * 64 + ch * 8) * 2, LA_ROW_BYTES, (unsigned int)(kw >> (ch * 8)) & 0xFFu, p.lr_scale);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float d = bf2f(f2bf(dv[j]));
+                            const float sg = 1.f / (1.f + __expf(-g[j]));
+                            du[j] = d * (g[j] * sg);
+                            dg[j] = d * u[j] * (sg * (1.f + g[j] * (1.f - sg)));
+                        }
+                        uint4 vg, vu;
+                        vg.x = pack_bf16(dg[0], dg[1]); vg.y = pack_bf16(dg[2], dg[3]); vg.z = pack_bf16(dg[4], dg[5]); vg.w = pack_bf16(dg[6], dg[7]);
+                        vu.x = pack_bf16(du[0], du[1]); vu.y = pack_bf16(du[2], du[3]); vu.z = pack_bf16(du[4], du[5]); vu.w = pack_bf16(du[6], du[7]);
+                        const int off = row * 128 + ((ch ^ (row & 7)) << 4);
+                        sts128(smem_u32(cdg) + off, vg);
+                        sts128(smem_u32(cdu) + off, vu);
+                    }
+                    if (sl == G2_BN / 128 - 1) {
+                        tc_fence_before();
+                        mbar_arrive_cluster(&tempty_bar[as], 0);
+                    }
+                    fence_proxy_async_smem();
+                    asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
+                    if (issuer) {
+                        tma_store_2d(&tmC, cdg, n0 + s * 64, m0);
+                        tma_store_2d(&tmC, cdu, I + n0 + s * 64, m0);
+                        tma_store_commit();
+                    }
+                }
+                continue;
+            }
             if constexpr (SWIGLU == 2) {
                 uint8_t* cdg = smem_cd;
                 uint8_t* cdu = smem_cd + CD_STAGE_BYTES;
@@ -168,6 +285,10 @@ gemm2_tcgen05_kernel(const GemmParams p,
                 const bf16* gurow = p.sw_gu + (size_t)(m_ok ? m : 0) * p.sw_ld;
 #pragma unroll 1
                 for (int s = 0; s < G2_BN / 64; ++s) {
+                    unsigned long long kw = ~0ull;
+                    if constexpr (LORA) {
+                        if (m_ok) kw = __ldg(p.lr_bits[0] + (size_t)((n0 >> 6) + s) * p.M + m);
+                    }
                     if (issuer) tma_store_wait_read<0>();
                     asm volatile("bar.sync 1, 128;" ::: "memory");
 #pragma unroll
@@ -185,11 +306,16 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         tmem_ld_wait();
 #pragma unroll
                         for (int c = 0; c < 4; ++c) {
-                            float g[8], u[8], dg[8], du[8];
+                            float g[8], u[8], dg[8], du[8], dv[8];
                             unpack8(gv[c], g); unpack8(uv[c], u);
 #pragma unroll
+                            for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
+                            if constexpr (LORA)
+                                lora_rank16_add8(dv, lt, la + (c0 + c * 8) * 2, LA_ROW_BYTES,
+                                                 (unsigned int)(kw >> (h * 32 + c * 8)) & 0xFFu, p.lr_scale);
+#pragma unroll
                             for (int j = 0; j < 8; ++j) {
-                                const float d = bf2f(f2bf(__uint_as_float(r[c * 8 + j]) * p.alpha));   // d(act) as the unfused path stores it
+                                const float d = bf2f(f2bf(dv[j]));                                     // d(act) as the unfused path stores it
                                 const float sg = 1.f / (1.f + __expf(-g[j]));
                                 const float si = g[j] * sg;
                                 du[j] = d * si;
@@ -269,9 +395,61 @@ gemm2_tcgen05_kernel(const GemmParams p,
                 continue;
             }
             uint8_t* cd = smem_cd + wg * CD_STAGE_BYTES;      // this warpgroup's staging buffer
+            if constexpr (LORA) {
+                // rolled over 8-column chunks (see the SwiGLU variant): ~0.9 k instructions per chunk body instead of 7 k unrolled
+#pragma unroll 1
+                for (int sl = 0; sl < G2_BN / 128; ++sl) {
+                    const int s = wg * (G2_BN / 128) + sl;
+                    unsigned long long kw[3];
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        kw[a] = ~0ull;
+                        if (a < p.lr_na && m_ok) kw[a] = __ldg(p.lr_bits[a] + (size_t)((n0 >> 6) + s) * p.M + m);
+                    }
+                    if (issuer) tma_store_wait_read<0>();
+                    asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
+#pragma unroll 1
+                    for (int ch = 0; ch < 8; ++ch) {
+                        uint32_t r8[8];
+                        tmem_ld8(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + s * 64 + ch * 8), r8);
+                        tmem_ld_wait();
+                        float v[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r8[j]) * p.alpha;
+#pragma unroll
+                        for (int a = 0; a < 3; ++a)
+                            if (a < p.lr_na)
+                                lora_rank16_add8(v, lt + a * 16, la + a * 16 * LA_ROW_BYTES + (sl * 64 + ch * 8) * 2, LA_ROW_BYTES,
+                                                 (unsigned int)(kw[a] >> (ch * 8)) & 0xFFu, p.lr_scale);
+                        uint4 u;
+                        u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);
+                        u.z = pack_bf16(v[4], v[5]); u.w = pack_bf16(v[6], v[7]);
+                        sts128(smem_u32(cd) + row * 128 + ((ch ^ (row & 7)) << 4), u);
+                    }
+                    if (sl == G2_BN / 128 - 1) {
+                        tc_fence_before();
+                        mbar_arrive_cluster(&tempty_bar[as], 0);
+                    }
+                    fence_proxy_async_smem();
+                    asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
+                    if (issuer) {
+                        tma_store_2d(&tmC, cd, n0 + s * 64, m0);
+                        tma_store_commit();
+                    }
+                }
+                continue;
+            }
 #pragma unroll 1
             for (int sl = 0; sl < G2_BN / 128; ++sl) {
                 const int s = wg * (G2_BN / 128) + sl;        // 64-column chunk index inside the tile
+                unsigned long long kw[LORA ? 3 : 1];
+                if constexpr (LORA) {
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        kw[a] = ~0ull;
+                        if (a < p.lr_na && m_ok) kw[a] = __ldg(p.lr_bits[a] + (size_t)((n0 >> 6) + s) * p.M + m);
+                    }
+                }
                 if (issuer) tma_store_wait_read<0>();
                 asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
 #pragma unroll
@@ -282,7 +460,8 @@ gemm2_tcgen05_kernel(const GemmParams p,
                     // bias / residual for these 32 columns are requested BEFORE the TMEM wait: issued inside the per-chunk loop
                     // each load sat behind the previous chunk's math and exposed a full memory latency
                     uint4 bv[4], rv[4];
-                    const bool has_bias = p.bias != nullptr, has_res = p.residual != nullptr && m_ok;
+                    // the dX GEMMs that carry the masked adapter term have no bias / residual: compiled out to keep registers
+                    const bool has_bias = !LORA && p.bias != nullptr, has_res = !LORA && p.residual != nullptr && m_ok;
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         const int nn = n + c * 8;
@@ -297,6 +476,13 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         float v[8];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
+                        if constexpr (LORA) {
+#pragma unroll
+                            for (int a = 0; a < 3; ++a)
+                                if (a < p.lr_na)
+                                    lora_rank16_add8(v, lt + a * 16, la + a * 16 * LA_ROW_BYTES + (sl * 64 + h * 32 + c * 8) * 2,
+                                                     LA_ROW_BYTES, (unsigned int)(kw[a] >> (h * 32 + c * 8)) & 0xFFu, p.lr_scale);
+                        }
                         if (has_bias) {
                             float b[8]; unpack8(bv[c], b);
 #pragma unroll

@@ -61,6 +61,10 @@ struct GemmParams {
     const bf16* sw_gu; int sw_ld;   // SWIGLU == 2: saved gate/up activations [M, 2I]
     int stages_used;        // pair kernel: ring depth actually used (<= G2_STAGES), tuning experiments
     int group_m;            // M-blocks swept together before moving to the next N-block (L2 residency of the A panel)
+    // pair kernel, LORA_EPI variants (dX under LoRA dropout): out[m, n] += lr_scale * sum_a keep_a[m, n] * (t_a[m, :] . A_a[:, n]),
+    // t [M, 16 lr_na] bf16, A [16 lr_na, N] bf16, keep bits as 64-bit words [N / 64][M] per adapter (lora_dropout.cu)
+    const bf16* lr_t; int lr_ldt; const bf16* lr_A; int lr_lda;
+    const unsigned long long* lr_bits[3]; int lr_na; float lr_scale;
 };
 
 __device__ __forceinline__ void tile_coords(int t, int mt, int nt, int GROUP_M, int& mb, int& nb) {
@@ -422,6 +426,10 @@ static int make_tmap(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1
     return 0;
 }
 
+int tmap2d_cached(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t stride_elems, uint32_t b0, uint32_t b1) {
+    return make_tmap(out, ptr, d0, d1, stride_elems, b0, b1);
+}
+
 int encode_tmap_bf16(CUtensorMap* out, const void* ptr, int rank, const unsigned long long* dims,
                      const unsigned long long* strides_bytes, const unsigned int* box) {
     PFN_encodeTiled enc = get_encode();
@@ -481,6 +489,9 @@ struct GemmArgs {
     float* ad_p = nullptr; float* ad_m = nullptr; float* ad_v = nullptr; void* ad_pb = nullptr; const float* ad_sumsq = nullptr;
     long long ad_ld = 0;
     float ad_lr = 0, ad_b1 = 0, ad_b2 = 0, ad_eps = 0, ad_wd = 0, ad_bc1 = 1, ad_bc2 = 1, ad_max_norm = 0, ad_gscale = 1, ad_two_lambda = 0;
+    // optional masked adapter term in the pair kernel's epilogue (LORA_EPI, see GemmParams)
+    const void* lr_t = nullptr; int lr_ldt = 0; const void* lr_A = nullptr; int lr_lda = 0;
+    const void* lr_bits[3] = {nullptr, nullptr, nullptr}; int lr_na = 0; float lr_scale = 1.f;
 };
 
 template <int BN, bool A_MN, bool B_MN, bool ADAM = false>
@@ -551,7 +562,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
 }
 
 // CTA-pair launch: 256 x 256 tiles, bf16 output, K-major A (the decoder / ViT / STC linears and their dX GEMMs).
-template <bool B_MN, int SWIGLU = 0>
+template <bool B_MN, int SWIGLU = 0, bool LORA = false>
 static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = nullptr, int ld_act = 0) {
     CUtensorMap tA1, tB1, tA2, tB2, tC, tAct;
     int rc;
@@ -588,8 +599,13 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     // halves the DRAM over-fetch (9.3 -> 4.5 GB per launch, ncu r01c) and is ~2 % faster under the power cap
     p.stages_used = a.K1 >= 24576 ? 4 : G2_STAGES;
     if (SWIGLU == 1) p.stages_used = G2_STAGES - 1;      // the last ring stage is the third epilogue staging buffer
-    { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES) p.stages_used = atoi(g); }
-    auto kern = gemm2_tcgen05_kernel<B_MN, SWIGLU>;
+    p.lr_t = reinterpret_cast<const bf16*>(a.lr_t); p.lr_ldt = a.lr_ldt; p.lr_A = reinterpret_cast<const bf16*>(a.lr_A); p.lr_lda = a.lr_lda;
+    for (int i = 0; i < 3; ++i) p.lr_bits[i] = reinterpret_cast<const unsigned long long*>(a.lr_bits[i]);
+    p.lr_na = a.lr_na; p.lr_scale = a.lr_scale;
+    if (LORA && p.stages_used > G2_STAGES - 1) p.stages_used = G2_STAGES - 1;   // the last ring stage holds the staged adapter A columns
+    if (LORA && SWIGLU == 2) p.stages_used = G2_STAGES - 2;                     // ... and one more the second warpgroup's staging buffers
+    { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES - (LORA && SWIGLU == 2 ? 2 : (LORA || SWIGLU == 1) ? 1 : 0)) p.stages_used = atoi(g); }
+    auto kern = gemm2_tcgen05_kernel<B_MN, SWIGLU, LORA>;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES);
@@ -600,7 +616,7 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     int cap = (a.max_ctas > 0 ? a.max_ctas : num_sms()) / 2;
     if (pairs > cap) pairs = cap;
     if (pairs < 1) pairs = 1;
-    kern<<<2 * pairs, g2_threads<SWIGLU>(), G2_SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC, tAct);
+    kern<<<2 * pairs, g2_threads<SWIGLU, LORA>(), G2_SMEM_BYTES, stream>>>(p, tA1, tB1, tA2, tB2, tC, tAct);
     return check_launch("gemm2_tcgen05_kernel");
 }
 
@@ -714,6 +730,47 @@ extern "C" int vlb_gemm_down_dx_swiglu_bwd(const void* dy, int lddy, const void*
     a.bias = nullptr; a.residual = nullptr; a.ldr = 0; a.act = 0;
     a.a_mn = 0; a.b_mn = 1; a.max_ctas = 0; a.split_k = 1;
     return vlb::launch_gemm2<true, 2>(a, reinterpret_cast<cudaStream_t>(stream), const_cast<void*>(gu), ldgu);
+}
+
+// dX GEMMs under LoRA dropout (pair kernel, LORA_EPI): out[M, N] = dy[M, K] W[K, N] + scale * sum_a keep_a . (t_a A_a), with
+// W the forward weight [out_features = K, in_features = N] read MN-major, t [M, 16 n_adapters] = s dy B (one 16-column group per
+// adapter), A [16 n_adapters, N] the stacked lora_A matrices and keep_a the adapter's dropout bits over its input [M, N].
+static int lora_args(vlb::GemmArgs& a, int M, int N, const void* t, int ldt, const void* A, int lda, int n_adapters,
+                     const void* b0, const void* b1, const void* b2, float scale) {
+    VLB_REQUIRE(n_adapters >= 1 && n_adapters <= 3 && t && A && b0 && (n_adapters < 2 || b1) && (n_adapters < 3 || b2),
+                "gemm lora epilogue: adapters=%d", n_adapters);
+    VLB_REQUIRE(N % 64 == 0 && ldt % 8 == 0 && lda % 8 == 0 && M > 0, "gemm lora epilogue: M=%d N=%d ldt=%d lda=%d", M, N, ldt, lda);
+    a.lr_t = t; a.lr_ldt = ldt; a.lr_A = A; a.lr_lda = lda; a.lr_bits[0] = b0; a.lr_bits[1] = b1; a.lr_bits[2] = b2;
+    a.lr_na = n_adapters; a.lr_scale = scale;
+    return 0;
+}
+
+extern "C" int vlb_gemm_dx_lora_masked(const void* dy, int lddy, const void* W, int ldw, void* out, int ldo, int M, int N, int K,
+                                       const void* t, int ldt, const void* A, int lda, int n_adapters, const void* bits0,
+                                       const void* bits1, const void* bits2, float scale, void* stream) {
+    VLB_REQUIRE(M > 0 && N > 0 && K > 0 && N % 8 == 0, "gemm_dx_lora_masked: M=%d N=%d K=%d", M, N, K);
+    vlb::GemmArgs a;
+    a.A1 = dy; a.lda1 = lddy; a.K1 = K; a.B1 = W; a.ldb1 = ldw;
+    a.A2 = nullptr; a.lda2 = 0; a.K2 = 0; a.B2 = nullptr; a.ldb2 = 0;
+    a.C = out; a.ldc = ldo; a.c_is_f32 = 0; a.accum = 0; a.M = M; a.N = N; a.alpha = 1.f;
+    a.bias = nullptr; a.residual = nullptr; a.ldr = 0; a.act = 0;
+    a.a_mn = 0; a.b_mn = 1; a.max_ctas = 0; a.split_k = 1;
+    if (lora_args(a, M, N, t, ldt, A, lda, n_adapters, bits0, bits1, bits2, scale)) return 1;
+    return vlb::launch_gemm2<true, 0, true>(a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int vlb_gemm_down_dx_swiglu_bwd_masked(const void* dy, int lddy, const void* wd, int ldw, const void* gu, int ldgu,
+                                                  void* dgu, int lddgu, int M, int I, int H, const void* t, int ldt, const void* A,
+                                                  int lda, const void* bits, float scale, void* stream) {
+    VLB_REQUIRE(M > 0 && I > 0 && I % 256 == 0 && H > 0 && ldgu % 8 == 0, "gemm_down_dx_swiglu_bwd_masked: M=%d I=%d H=%d ldgu=%d", M, I, H, ldgu);
+    vlb::GemmArgs a;
+    a.A1 = dy; a.lda1 = lddy; a.K1 = H; a.B1 = wd; a.ldb1 = ldw;
+    a.A2 = nullptr; a.lda2 = 0; a.K2 = 0; a.B2 = nullptr; a.ldb2 = 0;
+    a.C = dgu; a.ldc = lddgu; a.c_is_f32 = 0; a.accum = 0; a.M = M; a.N = I; a.alpha = 1.f;
+    a.bias = nullptr; a.residual = nullptr; a.ldr = 0; a.act = 0;
+    a.a_mn = 0; a.b_mn = 1; a.max_ctas = 0; a.split_k = 1;
+    if (lora_args(a, M, I, t, ldt, A, lda, 1, bits, nullptr, nullptr, scale)) return 1;
+    return vlb::launch_gemm2<true, 2, true>(a, reinterpret_cast<cudaStream_t>(stream), const_cast<void*>(gu), ldgu);
 }
 
 extern "C" void vlb_tmap_cache_clear() { vlb::tmap_cache_clear(); }

@@ -27,10 +27,12 @@ class Engine:
         self.T = trainables if trainables is not None else Trainables(cfg, self.dev)
         self.scale = cfg.lora_alpha / cfg.lora_r
         self.dropout_rate = float(dropout_rate)
-        # peft applies dropout to the adapter's INPUT: B(A(dropout(x))). With p > 0 the adapter branch can no longer ride in
-        # the base GEMM's accumulator on the way back (its input gradient needs the mask), so that mode costs one extra
-        # rank-r GEMM + masked add per projection input; p = 0 (benchmarks, parity) keeps the fully fused path.
+        # peft applies dropout to the adapter's INPUT: B(A(dropout(x))), one independent mask per adapter. With r = 16 the masks
+        # are packed bits applied inside the kernels that consume the masked values (csrc/lora_dropout.cu: no masked activation
+        # is ever written); other ranks fall back to materialised dropout(x) + a rank-r GEMM + masked add per projection input.
         self.lora_dropout = float(lora_dropout or 0.0)
+        self.masked_lora = cfg.lora_r == 16 and os.environ.get("VLB_LORA_MASKED", "1") != "0"
+        self.drop_bits = None       # test hook: dict filled with the packed keep masks keyed by (layer, site)
         self.drop_step = 0
         self.seed_mix = 0           # set_seed(seed, rank): every data-parallel rank draws its own dropout masks
         self.drop_masks = None      # test hook: dict filled with uint8 keep masks keyed by (layer, site)
@@ -190,8 +192,42 @@ class Engine:
     def set_seed(self, seed=0, rank=0):
         self.seed_mix = ((int(seed) & 0xFFFFFFFF) * 0x9E3779B1 + (int(rank) + 1) * 0x85EBCA77) & 0xFFFFFFFFFFFF
 
-    def _drop_seed(self, l, site):
-        return 0xD0C0FFEE + self.seed_mix + (self.drop_step << 12) + l * 4 + site
+    def _drop_seed(self, l, site, adapter=0):
+        return 0xD0C0FFEE + self.seed_mix + (self.drop_step << 16) + (l * 4 + site) * 4 + adapter
+
+    def _masked(self, training=True):
+        return training and self.lora_dropout > 0 and self.masked_lora
+
+    def _site_bits(self, l, site, n_ad, M, K, generate):
+        """Packed keep masks of the n_ad adapters reading projection input `site` of layer l: int64 [n_ad, K/64, M] (kept until
+        the backward of the same step, 1 bit per element)."""
+        bits = self.buf("L%d_dropbits%d" % (l, site), (n_ad, K // 64, M), torch.int64)
+        if generate:
+            for a in range(n_ad):
+                ops.dropout_bits(M, K, self.lora_dropout, self._drop_seed(l, site, a), bits[a])
+            self.launches += n_ad
+            if self.drop_bits is not None:
+                self.drop_bits[(l, site)] = bits
+        return [bits[a] for a in range(n_ad)]
+
+    def _lora_down(self, x, A, xa, l, site, training):
+        """xa = s * dropout(x) A^T for the adapters of one projection input (forward)."""
+        n_ad = A.shape[0] // self.cfg.lora_r
+        if self._masked(training):
+            bits = self._site_bits(l, site, n_ad, x.shape[0], x.shape[1], True)
+            ops.lora_down_masked(x, A, xa, bits, self.scale / (1.0 - self.lora_dropout))
+            self.launches += 1
+            return
+        self.gemm(self._lora_in(x, l, site, training), A, xa, alpha=self.scale)
+
+    def _lora_grad_a(self, t, x, gA, l, site):
+        """dA += t^T dropout(x) (backward)."""
+        if self._masked():
+            bits = self._site_bits(l, site, gA.shape[0] // self.cfg.lora_r, x.shape[0], x.shape[1], False)
+            ops.lora_grad_a_masked(x, t, gA, bits, 1.0 / (1.0 - self.lora_dropout))
+            self.launches += 1
+            return
+        self.gemm(t, self._lora_in_bwd(x, l, site), gA, a_mn=True, b_mn=True, out_f32=True, accumulate=True)
 
     def _lora_in(self, x, l, site, training):
         """Input of the LoRA A projection: x itself, or dropout(x) into a scratch buffer (regenerated in the backward)."""
@@ -219,6 +255,10 @@ class Engine:
         base GEMM, a rank-r GEMM and a masked add (the adapter's input gradient passes through the dropout mask)."""
         if self.lora_dropout <= 0:
             return self.gemm(dy, w_base, out, a2=t, b2=a_lora, b_mn=True)
+        if self._masked() and out.shape[1] % 64 == 0:
+            bits = self._site_bits(l, site, a_lora.shape[0] // self.cfg.lora_r, out.shape[0], out.shape[1], False)
+            self.launches += 1
+            return ops.gemm_dx_lora_masked(dy, w_base, out, t, a_lora, bits, 1.0 / (1.0 - self.lora_dropout))
         self.gemm(dy, w_base, out, b_mn=True)
         tmp = self.buf("lora_tmp_%d" % out.shape[1], tuple(out.shape))
         self.gemm(t, a_lora, tmp, b_mn=True)
@@ -240,23 +280,23 @@ class Engine:
             nxt = self.buf("L%d_x" % (l + 1), (M, cfg.hidden)) if save else self.buf("Lx_%d" % (l & 1), (M, cfg.hidden))
             ops.rmsnorm_fwd(x, L["ln1_w"], cfg.rms_eps, out=b["xn1"], rstd=b["rstd1"])
             if lora:
-                self.gemm(self._lora_in(b["xn1"], l, 0, save), T.w(p + "Acat_qkv"), b["xa1"], alpha=s)
+                self._lora_down(b["xn1"], T.w(p + "Acat_qkv"), b["xa1"], l, 0, save)
                 self.gemm(b["xn1"], L["wqkv"], b["qkv"], a2=b["xa1"], b2=bc["qkv"])
             else:
                 self.gemm(b["xn1"], L["wqkv"], b["qkv"])
             ops.rope_(b["qkv"], W.llm["cos"], W.llm["sin"], S, cfg.heads + cfg.kv_heads, D)
             ops.attn_fwd_into(b["qkv"], b["o"], b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True)
             if lora:
-                self.gemm(self._lora_in(b["o"], l, 1, save), T.w(p + "A_o"), b["xa2"], alpha=s)
+                self._lora_down(b["o"], T.w(p + "A_o"), b["xa2"], l, 1, save)
                 self.gemm(b["o"], L["wo"], b["h1"], a2=b["xa2"], b2=bc["o"], residual=x)
             else:
                 self.gemm(b["o"], L["wo"], b["h1"], residual=x)
             ops.rmsnorm_fwd(b["h1"], L["ln2_w"], cfg.rms_eps, out=b["xn2"], rstd=b["rstd2"])
             if lora:
-                self.gemm(self._lora_in(b["xn2"], l, 2, save), T.w(p + "Acat_gu"), b["xa3"], alpha=s)
+                self._lora_down(b["xn2"], T.w(p + "Acat_gu"), b["xa3"], l, 2, save)
             self.gateup(b["xn2"], L["wgu"], b["gu"], b["act"], b["xa3"] if lora else None, bc["gu"] if lora else None)
             if lora:
-                self.gemm(self._lora_in(b["act"], l, 3, save), T.w(p + "A_d"), b["xa4"], alpha=s)
+                self._lora_down(b["act"], T.w(p + "A_d"), b["xa4"], l, 3, save)
                 self.gemm(b["act"], L["wd"], nxt, a2=b["xa4"], b2=bc["d"], residual=b["h1"])
             else:
                 self.gemm(b["act"], L["wd"], nxt, residual=b["h1"])
@@ -290,26 +330,31 @@ class Engine:
             x = self.buf("L%d_x" % l, (M, H))
             # ---- down_proj: x_next = h1 + act Wd^T + s (act A_d^T) B_d^T
             self.gemm(dx, bc["d"], t16, b_mn=True, alpha=s)
-            fused_bwd = self.fuse_swiglu and self.lora_dropout <= 0 and I % 256 == 0 and M >= 256
-            if fused_bwd:                                   # d(act) stays in TMEM; dgu leaves the GEMM epilogue
+            masked = self._masked()
+            fused_bwd = self.fuse_swiglu and (self.lora_dropout <= 0 or masked) and I % 256 == 0 and M >= 256
+            if fused_bwd and masked:                        # the adapter's masked input gradient is added in the same epilogue
+                ops.gemm_down_dx_swiglu_bwd_masked(dx, L["wd"], b["gu"], dgu, t16, T.w(p + "A_d"),
+                                                   self._site_bits(l, 3, 1, M, I, False)[0], 1.0 / (1.0 - self.lora_dropout))
+                self.launches += 1
+            elif fused_bwd:                                 # d(act) stays in TMEM; dgu leaves the GEMM epilogue
                 self.down_dx_swiglu(dx, L["wd"], b["gu"], dgu, t16, T.w(p + "A_d"))
             else:
                 self._dx_with_lora(dx, L["wd"], t16, T.w(p + "A_d"), dact, l, 3)
-            self.gemm(t16, self._lora_in_bwd(b["act"], l, 3), T.g(p + "A_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self._lora_grad_a(t16, b["act"], T.g(p + "A_d"), l, 3)
             self.gemm(b["xa4"], dx, T.g(p + "Bt_d"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             if not fused_bwd:
                 ops.swiglu_bwd(b["gu"], dact, out=dgu)
             # ---- gate/up
             self.gemm(dgu, bc["gu"], t32, b_mn=True, alpha=s)
             self._dx_with_lora(dgu, L["wgu"], t32, T.w(p + "Acat_gu"), dxn, l, 2)
-            self.gemm(t32, self._lora_in_bwd(b["xn2"], l, 2), T.g(p + "Acat_gu"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self._lora_grad_a(t32, b["xn2"], T.g(p + "Acat_gu"), l, 2)
             self.gemm(b["xa3"][:, 0:r], dgu[:, 0:I], T.g(p + "Bt_g"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa3"][:, r:2 * r], dgu[:, I:2 * I], T.g(p + "Bt_u"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             ops.rmsnorm_bwd(dxn, b["h1"], L["ln2_w"], b["rstd2"], dres=dx, out=dh1)
             # ---- o_proj: h1 = x + o Wo^T + s (o A_o^T) B_o^T
             self.gemm(dh1, bc["o"], t16, b_mn=True, alpha=s)
             self._dx_with_lora(dh1, L["wo"], t16, T.w(p + "A_o"), do, l, 1)
-            self.gemm(t16, self._lora_in_bwd(b["o"], l, 1), T.g(p + "A_o"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self._lora_grad_a(t16, b["o"], T.g(p + "A_o"), l, 1)
             self.gemm(b["xa2"], dh1, T.g(p + "Bt_o"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             # ---- attention + RoPE
             ops.attn_bwd(b["qkv"], b["o"], do, b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True, dqkv=dqkv, dq_f32=dq32,
@@ -318,7 +363,7 @@ class Engine:
             ops.rope_(dqkv[:, nq:], W.llm["cos"], W.llm["sin"], S, cfg.kv_heads, D, inverse=True)
             # ---- q/k/v
             self.gemm(dqkv, bc["qkv"], t48, b_mn=True, alpha=s)
-            self.gemm(t48, self._lora_in_bwd(b["xn1"], l, 0), T.g(p + "Acat_qkv"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
+            self._lora_grad_a(t48, b["xn1"], T.g(p + "Acat_qkv"), l, 0)
             self.gemm(b["xa1"][:, 0:r], dqkv[:, 0:nq], T.g(p + "Bt_q"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)

@@ -317,3 +317,69 @@ def dropout_add(t, y, p, seed):
     M, K = t.shape
     _l.call("vlb_dropout_add", _l.ptr(t), t.stride(0), _l.ptr(y), y.stride(0), M, K, float(p), int(seed), _st())
     return y
+
+
+# ------------------------------------------------------------------------------------------------ LoRA dropout on the fused path
+def dropout_bits(n_tok, n_feat, p, seed, out):
+    """Keep mask of one adapter over its input [n_tok, n_feat] as packed bits: out int64 [n_feat // 64, n_tok]."""
+    assert out.dtype == torch.int64 and out.shape == (n_feat // 64, n_tok) and out.is_contiguous()
+    _l.call("vlb_dropout_bits", _l.ptr(out), int(n_tok), int(n_feat), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, _st())
+    return out
+
+
+def unpack_bits(bits):
+    """int64 [n_feat // 64, n_tok] -> uint8 keep mask [n_tok, n_feat] (tests: replay inside the oracle)."""
+    nfb, n_tok = bits.shape
+    sh = torch.arange(64, device=bits.device, dtype=torch.int64)
+    m = (bits[:, :, None] >> sh[None, None, :]) & 1                 # [fb, tok, 64]
+    return m.permute(1, 0, 2).reshape(n_tok, nfb * 64).to(torch.uint8)
+
+
+def _bits3(bits):
+    b = [_l.ptr(t) for t in bits] + [None, None]
+    return b[0], b[1], b[2]
+
+
+def lora_down_masked(x, A, xa, bits, alpha):
+    """xa[M, 16 n] = alpha * (keep_a . x) A_a^T for the n adapters sharing x; A [16 n, K] stacked, bits = list of n bit arrays."""
+    _chk(x, torch.bfloat16), _chk(A, torch.bfloat16), _chk(xa, torch.bfloat16)
+    M, K = x.shape
+    n = len(bits)
+    assert A.shape == (16 * n, K) and xa.shape == (M, 16 * n)
+    _l.call("vlb_lora_down_masked", _l.ptr(x), x.stride(0), _l.ptr(A), A.stride(0), _l.ptr(xa), xa.stride(0), M, K, n,
+            *_bits3(bits), float(alpha), _st())
+    return xa
+
+
+def lora_grad_a_masked(x, t, dA, bits, alpha):
+    """dA[16 n, K] += alpha * t_a^T (keep_a . x); x [M, K], t [M, 16 n], dA fp32."""
+    _chk(x, torch.bfloat16), _chk(t, torch.bfloat16), _chk(dA, torch.float32)
+    M, K = x.shape
+    n = len(bits)
+    assert t.shape == (M, 16 * n) and dA.shape == (16 * n, K)
+    _l.call("vlb_lora_grad_a_masked", _l.ptr(x), x.stride(0), _l.ptr(t), t.stride(0), _l.ptr(dA), dA.stride(0), M, K, n,
+            *_bits3(bits), float(alpha), _st())
+    return dA
+
+
+def gemm_dx_lora_masked(dy, W, out, t, A, bits, scale):
+    """out[M, N] = dy[M, K] @ W[K, N] + scale * sum_a keep_a . (t_a @ A_a)  (W = forward weight [out = K, in = N])."""
+    _chk(dy, torch.bfloat16), _chk(W, torch.bfloat16), _chk(out, torch.bfloat16), _chk(t, torch.bfloat16), _chk(A, torch.bfloat16)
+    M, K = dy.shape
+    N = W.shape[1]
+    n = len(bits)
+    assert W.shape[0] == K and out.shape == (M, N) and t.shape == (M, 16 * n) and A.shape == (16 * n, N)
+    _l.call("vlb_gemm_dx_lora_masked", _l.ptr(dy), dy.stride(0), _l.ptr(W), W.stride(0), _l.ptr(out), out.stride(0), M, N, K,
+            _l.ptr(t), t.stride(0), _l.ptr(A), A.stride(0), n, *_bits3(bits), float(scale), _st())
+    return out
+
+
+def gemm_down_dx_swiglu_bwd_masked(dy, wd, gu, dgu, t, A, bits, scale):
+    """dgu = swiglu_bwd(gu, dy @ wd + scale * keep . (t @ A)) from one CTA-pair GEMM launch (wd [H, I], A [16, I])."""
+    _chk(dy, torch.bfloat16), _chk(wd, torch.bfloat16), _chk(gu, torch.bfloat16), _chk(dgu, torch.bfloat16)
+    M, H = dy.shape
+    I = wd.shape[1]
+    assert wd.shape[0] == H and gu.shape == (M, 2 * I) and dgu.shape == (M, 2 * I) and t.shape == (M, 16) and A.shape == (16, I)
+    _l.call("vlb_gemm_down_dx_swiglu_bwd_masked", _l.ptr(dy), dy.stride(0), _l.ptr(wd), wd.stride(0), _l.ptr(gu), gu.stride(0),
+            _l.ptr(dgu), dgu.stride(0), M, I, H, _l.ptr(t), t.stride(0), _l.ptr(A), A.stride(0), _l.ptr(bits), float(scale), _st())
+    return dgu

@@ -1,5 +1,5 @@
 """Per-entry-point time breakdown of one 7B training step (CUDA events around every C-ABI call, in situ).
-usage: python tools/breakdown.py [B] [warmup]   -- prints a table; GEMMs are classed by shape role."""
+usage: python tools/breakdown.py [B] [warmup] [lora_dropout] [head_dropout]   -- prints a table; GEMMs are classed by shape role."""
 import collections
 import os
 import sys
@@ -11,7 +11,8 @@ from phantom_vlb_b200.litmodule import VLBLitModule
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 4
 warm = int(sys.argv[2]) if len(sys.argv) > 2 else 3
-cfg = lit_config()
+cfg = lit_config(lora_dropout=float(sys.argv[3]) if len(sys.argv) > 3 else 0.0,
+                 dropout_rate=float(sys.argv[4]) if len(sys.argv) > 4 else 0.0)
 m = VLBLitModule(cfg)
 m.configure_model(device=torch.device("cuda", 0))
 batch = {k: v.cuda() for k, v in host_batches(m.model_config, B, 1, 1234)[0].items()}
@@ -31,6 +32,10 @@ rows = lib.profile_end()
 agg = collections.defaultdict(lambda: [0, 0.0, 0.0])
 for name, ms, a in rows:
     fl = 0.0
+    if name == "vlb_gemm_dx_lora_masked":
+        name += "[N=%d,K=%d,na=%d]" % (a[7], a[8], a[13])
+    if name in ("vlb_lora_down_masked", "vlb_lora_grad_a_masked"):
+        name += "[K=%d,na=%d]" % (a[7], a[8])
     if name == "vlb_gemm_bf16":
         M, N, K, K2, f32 = a[6], a[7], a[8], a[13] if a[9] else 0, a[21]
         fl = 2.0 * M * N * (K + K2)
