@@ -169,7 +169,8 @@ class STCConnector(nn.Module):
 class RefVLB(nn.Module):
     """Backbone + brain head of VLBLitModule (LoRA mode), fp32 on CPU."""
 
-    def __init__(self, cfg: RefConfig, seed: int = 1234, lora_b_std: float = 0.02):
+    def __init__(self, cfg: RefConfig, seed: int = 1234, lora_b_std: float = 0.02, lora_dropout: float = 0.0,
+                 head_dropout: float = 0.0):
         super().__init__()
         from transformers import CLIPVisionConfig, CLIPVisionModel, MistralConfig, MistralModel
         self.cfg = cfg
@@ -192,7 +193,7 @@ class RefVLB(nn.Module):
         for layer in self.llm.layers:
             for name in LORA_TARGETS:
                 parent = layer.self_attn if name in ("q_proj", "k_proj", "v_proj", "o_proj") else layer.mlp
-                setattr(parent, name, LoraLinear(getattr(parent, name), cfg.lora_r, cfg.lora_alpha))
+                setattr(parent, name, LoraLinear(getattr(parent, name), cfg.lora_r, cfg.lora_alpha, lora_dropout))
         if lora_b_std > 0:      # parity runs exercise the adapter path with a non-zero B (SURVEY 8c golden generation)
             g = torch.Generator().manual_seed(seed + 1)
             for m in self.modules():
@@ -202,6 +203,7 @@ class RefVLB(nn.Module):
         self.layer_norm1 = nn.LayerNorm(cfg.hidden)
         self.layer_norm2 = nn.LayerNorm(cfg.hidden)
         self.ridge = nn.Linear(cfg.hidden, cfg.num_target, bias=True)
+        self.dropout = nn.Dropout(head_dropout) if head_dropout > 0 else nn.Identity()      # litmodule.py:226
 
     # ---- encoder.py:31-53
     def encode_frames(self, frames):
@@ -260,7 +262,7 @@ class RefVLB(nn.Module):
     def head(self, hidden, weight_mask):
         h = self.layer_norm1(hidden)
         pooled = torch.einsum("bse,bs->be", h, weight_mask)        # src/utils.py:56
-        hrf = self.layer_norm2(pooled)
+        hrf = self.dropout(self.layer_norm2(pooled))
         pred = self.ridge(hrf)
         l2 = self.cfg.l2_lambda * torch.norm(self.ridge.weight, p=2) ** 2     # src/utils.py:70
         return pred, l2, pooled, hrf

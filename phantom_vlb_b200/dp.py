@@ -105,3 +105,40 @@ def make_sum_reducer(group=None):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
         return t
     return reduce
+
+
+class OverlappedGradReducer:
+    """Engine.grad_ready target: all-reduces every finished slice of the flat gradient on a side stream while the backward of the
+    earlier decoder layers is still running ('launch per-chunk all-reduces as backward finishes each group of
+    layers'). `wait()` makes the compute stream wait for the last one; it must be called before the optimiser kernels."""
+
+    def __init__(self, group=None, device=None, timing=False):
+        self.group, self.timing = group, timing
+        self.stream = torch.cuda.Stream(device)
+        self.spans = []                     # (start, end) events of each all-reduce on the side stream (timing=True)
+        self.bytes = 0
+
+    def __call__(self, flat_slice):
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
+            return
+        ready = torch.cuda.Event()
+        ready.record()                      # on the compute stream: everything that writes this slice has been enqueued
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ready)
+            if self.timing:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(self.stream)
+            dist.all_reduce(flat_slice, op=dist.ReduceOp.SUM, group=self.group)
+            if self.timing:
+                e1.record(self.stream)
+                self.spans.append((e0, e1))
+        self.bytes += flat_slice.numel() * flat_slice.element_size()
+
+    def wait(self):
+        torch.cuda.current_stream().wait_stream(self.stream)
+
+    def pop_ms(self):
+        """Sum of the all-reduce durations recorded since the last call (synchronise first)."""
+        ms = sum(e0.elapsed_time(e1) for e0, e1 in self.spans)
+        self.spans = []
+        return ms

@@ -42,6 +42,11 @@ class Engine:
         self.fused_head_opt = self.T.num_target_local * cfg.hidden >= (1 << 26)
         self.shard_reduce = None    # callable(tensor): in-place sum across voxel shards of the readout head (config 4)
         self.row_gather = None      # callable(tensor) -> rows of all ranks (dp.gather_rows): replicated wide head under DP
+        # data parallel overlap: callable(flat gradient slice) invoked as soon as a slice of T.grad is final -- the head's
+        # right after the head backward, then groups of `grad_chunk_layers` decoder layers as the backward leaves them
+        # (dp.OverlappedGradReducer all-reduces each on a side stream, so only the last group is exposed)
+        self.grad_ready = None
+        self.grad_chunk_layers = 4
         self.launches = 0
         self.profile = None
         self.fuse_swiglu = os.environ.get("VLB_FUSE_SWIGLU", "1") != "0"
@@ -71,6 +76,18 @@ class Engine:
         a2 = kw.get("a2")
         K2 = 0 if a2 is None else (a2.shape[0] if kw.get("a_mn") else a2.shape[1])
         self.profile.append((e0, e1, 2.0 * M * N * (K + K2), (M, N, K, K2)))
+        return r
+
+    def _timed(self, flops, shape, fn):
+        """Run one launch; in the instrumented pass (bench.py roofline) bracket it with CUDA events and record its algorithmic FLOPs."""
+        self.launches += 1
+        if self.profile is None:
+            return fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = fn()
+        e1.record()
+        self.profile.append((e0, e1, flops, shape))
         return r
 
     def gateup(self, x, wgu, gu, act, a2, b2):
@@ -257,8 +274,9 @@ class Engine:
             return self.gemm(dy, w_base, out, a2=t, b2=a_lora, b_mn=True)
         if self._masked() and out.shape[1] % 64 == 0:
             bits = self._site_bits(l, site, a_lora.shape[0] // self.cfg.lora_r, out.shape[0], out.shape[1], False)
-            self.launches += 1
-            return ops.gemm_dx_lora_masked(dy, w_base, out, t, a_lora, bits, 1.0 / (1.0 - self.lora_dropout))
+            M, N, K = out.shape[0], out.shape[1], dy.shape[1]
+            return self._timed(2.0 * M * N * (K + t.shape[1]), (M, N, K, t.shape[1]),
+                               lambda: ops.gemm_dx_lora_masked(dy, w_base, out, t, a_lora, bits, 1.0 / (1.0 - self.lora_dropout)))
         self.gemm(dy, w_base, out, b_mn=True)
         tmp = self.buf("lora_tmp_%d" % out.shape[1], tuple(out.shape))
         self.gemm(t, a_lora, tmp, b_mn=True)
@@ -333,9 +351,10 @@ class Engine:
             masked = self._masked()
             fused_bwd = self.fuse_swiglu and (self.lora_dropout <= 0 or masked) and I % 256 == 0 and M >= 256
             if fused_bwd and masked:                        # the adapter's masked input gradient is added in the same epilogue
-                ops.gemm_down_dx_swiglu_bwd_masked(dx, L["wd"], b["gu"], dgu, t16, T.w(p + "A_d"),
-                                                   self._site_bits(l, 3, 1, M, I, False)[0], 1.0 / (1.0 - self.lora_dropout))
-                self.launches += 1
+                bits3 = self._site_bits(l, 3, 1, M, I, False)[0]
+                self._timed(2.0 * M * I * (H + r), (M, I, H, r),
+                            lambda: ops.gemm_down_dx_swiglu_bwd_masked(dx, L["wd"], b["gu"], dgu, t16, T.w(p + "A_d"), bits3,
+                                                                       1.0 / (1.0 - self.lora_dropout)))
             elif fused_bwd:                                 # d(act) stays in TMEM; dgu leaves the GEMM epilogue
                 self.down_dx_swiglu(dx, L["wd"], b["gu"], dgu, t16, T.w(p + "A_d"))
             else:
@@ -368,6 +387,13 @@ class Engine:
             self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.launches += 6 if fused_bwd else 7
+            if self.grad_ready is not None and l % self.grad_chunk_layers == 0:
+                hi_l = min(cfg.layers, l + self.grad_chunk_layers)
+                lo = T.offsets["layers.%d.Acat_qkv" % l][0]
+                hi = T.offsets["layers.%d.Acat_qkv" % hi_l][0] if hi_l < cfg.layers else T.offsets["ridge_w"][0]
+                # every kernel that writes these layers' slice of T.grad has been enqueued above (the q/k/v input-gradient GEMM
+                # and the RMSNorm backward below do not touch it)
+                self.grad_ready(T.grad[lo:hi])
             if l > 0:        # the spliced embeddings are frozen: layer 0 needs no input gradient
                 self._dx_with_lora(dqkv, L["wqkv"], t48, T.w(p + "Acat_qkv"), dxn, l, 0)
                 nxt = dxa if dx.data_ptr() != dxa.data_ptr() else dxb
@@ -514,6 +540,8 @@ class Engine:
         y = batch["timeseries"].contiguous()
         out, pred = self.head_forward(hidden, wm, y, B, training=True)
         dx = self.head_backward(hidden, wm, B, need_dx=lora)
+        if self.grad_ready is not None and not self.fused_head_opt:
+            self.grad_ready(self.T.grad[self.T.offsets["ridge_w"][0]:])     # ridge W/b, LN1, LN2: final before the decoder backward
         if lora:
             self.decoder_backward(dx, B)
         return out, pred
@@ -560,7 +588,8 @@ class Engine:
 
     def optimizer_step(self, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, max_norm=1.0, world_size=1,
                        allreduce=None):
-        """clip_grad_norm_(max_norm) + AdamW on the flat buffer; `allreduce(tensor)` sums gradients across ranks first."""
+        """clip_grad_norm_(max_norm) + AdamW on the flat buffer; `allreduce(tensor)` sums gradients across ranks first (pass
+        None with world_size > 1 when the slices were already summed through `grad_ready`)."""
         T = self.T
         fused = self.fused_head_opt
         off_w, shape_w = T.offsets["ridge_w"]

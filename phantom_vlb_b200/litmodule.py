@@ -94,7 +94,11 @@ class _StepFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
-        return ctx.module.engine.T.grad * g, None, None
+        eng = ctx.module.engine
+        wait = getattr(eng.grad_ready, "wait", None)
+        if wait is not None:                       # overlapped data-parallel reduction (dp.OverlappedGradReducer): let it land
+            wait()
+        return eng.T.grad * g, None, None
 
 
 class FusedClipAdamW(torch.optim.Optimizer):
@@ -104,6 +108,7 @@ class FusedClipAdamW(torch.optim.Optimizer):
         super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay))
         self.engine, self.max_norm, self.world_size = engine, max_norm, world_size
         self.allreduce = None       # set to a callable(tensor) to sum gradients across ranks outside Lightning's DDP
+        self.prereduced = False     # True: gradients were already SUMMED across world_size ranks (engine.grad_ready reducer)
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -115,14 +120,16 @@ class FusedClipAdamW(torch.optim.Optimizer):
         p = grp["params"][0]
         T = self.engine.T
         if torch.distributed.is_available() and torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1 \
-                and self.engine.fused_head_opt and self.engine.shard_reduce is None and self.allreduce is None:
+                and self.engine.fused_head_opt and self.engine.shard_reduce is None and self.allreduce is None \
+                and not self.prereduced:
             raise RuntimeError("wide replicated readout head under DDP: its rank-B gradient is not part of flat.grad; shard the "
                                "head by voxel (target_slice + engine.shard_reduce) or set optimizer.allreduce + "
                                "engine.row_gather")
         if p.grad is not None and p.grad.data_ptr() != T.grad.data_ptr():
             T.grad.copy_(p.grad)
         self.engine.optimizer_step(grp["lr"], betas=grp["betas"], eps=grp["eps"], weight_decay=grp["weight_decay"],
-                                   max_norm=self.max_norm, world_size=self.world_size if self.allreduce else 1,
+                                   max_norm=self.max_norm,
+                                   world_size=self.world_size if (self.allreduce or self.prereduced) else 1,
                                    allreduce=self.allreduce)                 # under DDP p.grad is already averaged
         return loss
 

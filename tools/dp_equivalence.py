@@ -1,0 +1,105 @@
+"""N ranks x B clips through NCCL == 1 rank x N*B clips, on hardware:
+
+    torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/dp_equivalence.py
+
+Every rank builds the same model (seed 1234, dropout 0 so both paths are deterministic). Data-parallel path: rank r steps its
+own B clips with the overlapped chunked all-reduce (dp.OverlappedGradReducer) and the fused clip + AdamW at grad_scale 1/N.
+Reference path: the same rank also steps a second engine (sharing the frozen weights) on ALL N*B clips alone. Compared: the
+flat gradient (sum over ranks / N vs single) and the parameters after the optimiser step, as relative Frobenius errors --
+fp32 reduction-order noise only. Scenario 2 repeats it with a wide replicated readout head (P = 16384), where the rank-B
+ridge gradient is never materialised (fused_head_opt): the ranks exchange dpred / hrf rows instead (engine.row_gather).
+Rank 0 prints one JSON line per scenario."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from bench import collate
+from phantom_vlb_b200 import dp
+from phantom_vlb_b200.datamodule import SyntheticVLBDataset
+from phantom_vlb_b200.engine import Engine
+from phantom_vlb_b200.model import ModelConfig, Trainables, frozen_random
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).norm() / (b.double().norm() + 1e-30))
+
+
+def scenario(name, mc, B, rank, world, dev, W):
+    def make():
+        T = Trainables(mc, dev)
+        T.init_default(1234, lora_b_std=0.02)
+        return Engine(mc, W, T, device=dev)
+    ds = SyntheticVLBDataset(mc, length=world * B, seed=99)
+    full = {k: v.to(dev) for k, v in collate([ds[i] for i in range(world * B)]).items()}
+    mine = {k: v[rank * B:(rank + 1) * B].contiguous() for k, v in full.items()}
+    # ---- data parallel
+    e_dp = make()
+    overlapped = not e_dp.fused_head_opt
+    reducer = dp.OverlappedGradReducer(device=dev) if overlapped else None
+    e_dp.grad_ready = reducer
+    e_dp.row_gather = dp.gather_rows
+    out_dp, _ = e_dp.loss_and_grads(mine)
+    if overlapped:
+        reducer.wait()
+        g_dp = e_dp.T.grad.clone() / world
+        e_dp.optimizer_step(1e-3, world_size=world)
+    else:
+        e_dp.optimizer_step(1e-3, world_size=world, allreduce=lambda t: dist.all_reduce(t))
+        g_dp = e_dp.T.grad.clone() / world
+    loss_dp = out_dp[0].clone()
+    dist.all_reduce(loss_dp)
+    loss_dp = float(loss_dp) / world
+    # ---- single process, all clips
+    e_1 = make()
+    out_1, _ = e_1.loss_and_grads(full)
+    g_1 = e_1.T.grad.clone()
+    e_1.optimizer_step(1e-3)
+    torch.cuda.synchronize()
+    off_w, shape_w = e_1.T.offsets["ridge_w"]
+    n_w = shape_w[0] * shape_w[1]
+    keep = torch.ones(e_1.T.numel, dtype=torch.bool, device=dev)
+    if e_1.fused_head_opt:
+        keep[off_w:off_w + n_w] = False         # never materialised on this route: compared through the parameters
+    res = dict(scenario=name, n_gpus=world, clips_per_rank=B, fused_head_opt=bool(e_1.fused_head_opt), overlapped_allreduce=overlapped,
+               loss_dp_mean=loss_dp, loss_single=float(out_1[0]), grad_rel_err=rel(g_dp[keep], g_1[keep]),
+               param_rel_err=rel(e_dp.T.param, e_1.T.param),
+               update_rel_err=rel(e_dp.T.param - make().T.param, e_1.T.param - make().T.param),
+               ridge_update_rel_err=rel((e_dp.T.param - make().T.param)[off_w:off_w + n_w], (e_1.T.param - make().T.param)[off_w:off_w + n_w]))
+    # replicas must hold bit-identical parameters after the step
+    p0 = e_dp.T.param.clone()
+    dist.broadcast(p0, 0)
+    res["replicas_bit_identical"] = bool(torch.equal(p0, e_dp.T.param))
+    ok = torch.tensor([int(res["replicas_bit_identical"])], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    res["replicas_bit_identical"] = bool(int(ok))
+    if rank == 0:
+        print(json.dumps(res), flush=True)
+    assert abs(loss_dp - res["loss_single"]) < 2e-3 * abs(res["loss_single"]), res
+    assert res["grad_rel_err"] < 2e-2 and res["update_rel_err"] < 5e-2 and res["replicas_bit_identical"], res
+    del e_dp, e_1
+    torch.cuda.empty_cache()
+
+
+def main():
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    mc = ModelConfig()                                        # full VideoLLaMA2-7B, P = 1000 (BASELINE configs[2])
+    W = frozen_random(mc, dev, 1234)
+    scenario("7B_lora_dp", mc, 2, rank, world, dev, W)
+    mc2 = ModelConfig(vit_layers=2, layers=2, num_target=16384)      # reduced depth, wide replicated head: fused_head_opt
+    W2 = frozen_random(mc2, dev, 1234)
+    scenario("wide_replicated_head", mc2, 2, rank, world, dev, W2)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

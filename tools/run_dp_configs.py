@@ -50,12 +50,13 @@ def timed(fn, warm, it, world, dev):
     return float(ms)
 
 
-def c4(B=4, P=250000):
+def measure_c4(rank, world, dev, B=4, P=250000, W=None, out=print):
+    """BASELINE configs[3] on `world` ranks; `W` = an already resident frozen 7B replica (bench.py passes its own)."""
     from phantom_vlb_b200.engine import Engine
     from phantom_vlb_b200.model import ModelConfig, Trainables, frozen_random
-    rank, world, dev = setup()
     mc = ModelConfig(num_frames=16, num_target=P, use_lora=False)
-    W = frozen_random(mc, dev, 1234)                       # identical frozen replica on every rank
+    if W is None:
+        W = frozen_random(mc, dev, 1234)                   # identical frozen replica on every rank
     lo, hi = dp.shard_columns(P, rank, world)
     T = Trainables(mc, dev, target_slice=(lo, hi))
     T.init_default(1234 + rank)
@@ -66,7 +67,7 @@ def c4(B=4, P=250000):
     sw = torch.empty((B,), device=dev)
     ms_f = timed(lambda: eng.extract_features(batch, out_u=u, out_sw=sw), 2, 4, world, dev)
     if rank == 0:
-        print(json.dumps(dict(kind="c4_extract_features", n_gpus=world, clips_per_gpu=B, frames=16, ms=round(ms_f, 2),
+        out(json.dumps(dict(kind="c4_extract_features", n_gpus=world, clips_per_gpu=B, frames=16, ms=round(ms_f, 2),
                               clips_per_s=round(world * B / ms_f * 1e3, 2), tflops_per_gpu=round(39.0 * B / ms_f * 1e3, 1))), flush=True)
     g = torch.Generator(device=dev).manual_seed(99)        # same targets on every rank; each keeps its voxel columns
     y_all = torch.randn((world * B, P), device=dev, generator=g)
@@ -82,7 +83,7 @@ def c4(B=4, P=250000):
     loss = float(eng.buf("hd_loss", (3,), torch.float32)[0])
     if rank == 0:
         per_rank = 34 * mc.hidden * (hi - lo)              # 6 B/param head traffic + 28 B/param AdamW
-        print(json.dumps(dict(kind="c4_sharded_head_step", n_gpus=world, samples=world * B, P=P, voxels_per_gpu=hi - lo,
+        out(json.dumps(dict(kind="c4_sharded_head_step", n_gpus=world, samples=world * B, P=P, voxels_per_gpu=hi - lo,
                               ms=round(ms_h, 3), loss=loss, alg_GB_per_gpu=round(per_rank / 1e9, 2),
                               achieved_GBs_per_gpu=round(per_rank / ms_h / 1e6, 1))), flush=True)
     # sharded == unsharded: same features, small head, rank 0 holds the full one
@@ -109,15 +110,20 @@ def c4(B=4, P=250000):
     err = abs(l_sh - l_full) / abs(l_full)
     gerr = float((g_sh - g_full).norm() / g_full.norm())
     if rank == 0:
-        print(json.dumps(dict(kind="c4_sharded_vs_unsharded", n_gpus=world, loss_rel_err=err, ln2_grad_rel_err=gerr)), flush=True)
+        out(json.dumps(dict(kind="c4_sharded_vs_unsharded", n_gpus=world, loss_rel_err=err, ln2_grad_rel_err=gerr)), flush=True)
     assert err < 1e-5 and gerr < 1e-3
+
+
+def c4(B=4, P=250000):
+    rank, world, dev = setup()
+    measure_c4(rank, world, dev, B, P)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
-def c5(N=22528, P=250000):
-    rank, world, dev = setup()
+def measure_c5(rank, world, dev, N=22528, P=250000, out=print):
+    """BASELINE configs[4]: rows of the held-out season sharded over the ranks, fp64 moments merged with one all-reduce."""
     rows = N // world + (1 if rank < N % world else 0)      # ragged row shards
     g = torch.Generator(device=dev).manual_seed(3 + rank)
     x = torch.randn((rows, P), device=dev, generator=g)
@@ -136,9 +142,14 @@ def c5(N=22528, P=250000):
     r = res["r"]
     if rank == 0:
         nbytes = 2 * N * P * 4
-        print(json.dumps(dict(kind="c5_pearson_row_sharded", n_gpus=world, N=N, P=P, ms=round(ms, 3), alg_GB=round(nbytes / 1e9, 2),
+        out(json.dumps(dict(kind="c5_pearson_row_sharded", n_gpus=world, N=N, P=P, ms=round(ms, 3), alg_GB=round(nbytes / 1e9, 2),
                               aggregate_GBs=round(nbytes / ms / 1e6, 1), mean_r=float(r.mean()), expect_r=round(0.5 / 1.25 ** 0.5, 4))), flush=True)
     assert abs(float(r.mean()) - 0.5 / 1.25 ** 0.5) < 5e-3
+
+
+def c5(N=22528, P=250000):
+    rank, world, dev = setup()
+    measure_c5(rank, world, dev, N, P)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
