@@ -173,6 +173,8 @@ def run_ours(args):
     # stream while the backward of the earlier layers runs; only the last group is exposed
     reducer = dp.OverlappedGradReducer(device=dev, timing=True) if world > 1 else None
     eng.grad_ready = reducer
+    if world > 1:
+        eng.row_gather, eng.bcast0 = dp.gather_rows, (lambda t: dist.broadcast(t, 0))
 
     def barrier():
         if world > 1:

@@ -93,6 +93,26 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
     return r;
 }
 
+// Deterministic grid-wide sum into *acc: every block parks its partial, the LAST block to finish adds them in block order. A
+// plain atomicAdd per block makes the low bits depend on the arrival order -- data-parallel replicas then compute clip
+// coefficients that differ in the last place and their parameters drift apart bit by bit.
+struct DetSumWs { float partial[4096]; unsigned int count; };
+__device__ __forceinline__ void det_grid_add(DetSumWs& ws, float s /* valid in thread 0 */, float* acc, float* red) {
+    __shared__ bool last;
+    if (threadIdx.x == 0) {
+        ws.partial[blockIdx.x] = s;
+        __threadfence();
+        last = atomicAdd(&ws.count, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    float t = 0.f;
+    for (unsigned int i = threadIdx.x; i < gridDim.x; i += blockDim.x) t += reinterpret_cast<volatile float*>(ws.partial)[i];
+    t = block_sum(t, red);
+    if (threadIdx.x == 0) { *acc += t; ws.count = 0; }
+}
+
 // ---------------------------------------------------------------- activations
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
 __device__ __forceinline__ float siluf_(float x) { return x * sigmoidf_(x); }

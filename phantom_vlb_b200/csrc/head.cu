@@ -426,6 +426,8 @@ __global__ void ln1_affine_bwd_kernel(const float* __restrict__ dpooled, const f
 //   2 <dpred^T hrf, 2 lambda W> = 4 lambda sum_{n,p} dpred[n,p] * (pred[n,p] - b[p])      (pred - b = hrf W^T)
 //   ||2 lambda W||^2 = 4 lambda^2 * wsq
 // sumsq += all three. grid-stride over the N x P elements for the cross term; block 0 adds the Gram and W terms.
+__device__ DetSumWs g_gradnorm_ws;
+
 __global__ void head_gradnorm_kernel(const bf16* __restrict__ dpred, const bf16* __restrict__ pred, const bf16* __restrict__ bias,
                                      const float* __restrict__ gd, const float* __restrict__ gh, const float* __restrict__ wsq,
                                      float* __restrict__ sumsq, int N, int ldg, long long P, float lambda) {
@@ -444,7 +446,7 @@ __global__ void head_gradnorm_kernel(const bf16* __restrict__ dpred, const bf16*
         if (threadIdx.x == 0) s += 4.f * lambda * lambda * wsq[0];
     }
     s = block_sum(s, red);
-    if (threadIdx.x == 0) atomicAdd(sumsq, s);
+    det_grid_add(g_gradnorm_ws, s, sumsq, red);
 }
 
 // ---- HRFConvolveLayer on its own (src/utils.py:40-56): out[b, e] = sum_s w[b, s] * emb[b, s, e].

@@ -8,6 +8,8 @@
 
 namespace vlb {
 
+__device__ DetSumWs g_sumsq_ws;
+
 __global__ void sumsq_kernel(const float* __restrict__ g, long long n4, float* __restrict__ acc) {
     __shared__ float red[32];
     float s = 0.f;
@@ -16,7 +18,7 @@ __global__ void sumsq_kernel(const float* __restrict__ g, long long n4, float* _
         s += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
     s = block_sum(s, red);
-    if (threadIdx.x == 0) atomicAdd(acc, s);
+    det_grid_add(g_sumsq_ws, s, acc, red);
 }
 
 struct AdamArgs {

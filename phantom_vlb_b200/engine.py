@@ -42,6 +42,7 @@ class Engine:
         self.fused_head_opt = self.T.num_target_local * cfg.hidden >= (1 << 26)
         self.shard_reduce = None    # callable(tensor): in-place sum across voxel shards of the readout head (config 4)
         self.row_gather = None      # callable(tensor) -> rows of all ranks (dp.gather_rows): replicated wide head under DP
+        self.bcast0 = None          # callable(tensor): broadcast from rank 0 (same case: one clip norm for all replicas)
         # data parallel overlap: callable(flat gradient slice) invoked as soon as a slice of T.grad is final -- the head's
         # right after the head backward, then groups of `grad_chunk_layers` decoder layers as the backward leaves them
         # (dp.OverlappedGradReducer all-reduces each on a side stream, so only the last group is exposed)
@@ -647,6 +648,10 @@ class Engine:
                     N8, _l.ptr(self.buf("hd_wsq_local", (1,), torch.float32)), _l.ptr(T.sumsq), N, T.num_target_local,
                     lam, st)
             self.launches += 1
+        if dp_rows is not None and self.bcast0 is not None:
+            # the Gram GEMMs above are split-K (red.add: summation order varies), so each replica's norm differs in its last bits;
+            # rank 0's value is used everywhere to keep the replicas bit-identical
+            self.bcast0(T.sumsq)
         if self.shard_reduce is not None:
             # voxel-sharded head: ridge W/b gradients are rank-private (sum their squares across ranks), the LN1/LN2
             # gradients that follow them in the flat buffer are replicated (count them once)

@@ -42,6 +42,7 @@ def scenario(name, mc, B, rank, world, dev, W):
     reducer = dp.OverlappedGradReducer(device=dev) if overlapped else None
     e_dp.grad_ready = reducer
     e_dp.row_gather = dp.gather_rows
+    e_dp.bcast0 = lambda t: dist.broadcast(t, 0)
     out_dp, _ = e_dp.loss_and_grads(mine)
     if overlapped:
         reducer.wait()
@@ -79,7 +80,9 @@ def scenario(name, mc, B, rank, world, dev, W):
     if rank == 0:
         print(json.dumps(res), flush=True)
     assert abs(loss_dp - res["loss_single"]) < 2e-3 * abs(res["loss_single"]), res
-    assert res["grad_rel_err"] < 2e-2 and res["update_rel_err"] < 5e-2 and res["replicas_bit_identical"], res
+    # the first AdamW step is sign-like (m / sqrt(v) = +-1): gradient elements within reduction noise of zero flip their update,
+    # so the update error is an order of magnitude above the gradient error by construction
+    assert res["grad_rel_err"] < 2e-2 and res["update_rel_err"] < 0.15 and res["replicas_bit_identical"], res
     del e_dp, e_1
     torch.cuda.empty_cache()
 
