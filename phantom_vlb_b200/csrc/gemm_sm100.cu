@@ -595,9 +595,13 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     // while B streams past it. Measured sustained at M=16384: K=4096 shapes +1.5..3 % at 16, K >= 14336 shapes best at 8.
     p.group_m = a.K1 <= 8192 ? 16 : 8;
     { const char* g = getenv("VLB_GEMM_GROUP_M"); if (g && atoi(g) > 0) p.group_m = atoi(g); }
-    // ring depth: 6 keeps the tensor pipe 95-99 % busy; for the longest contraction (K = 28672, dX of gate/up) a 4-deep ring
-    // halves the DRAM over-fetch (9.3 -> 4.5 GB per launch, ncu r01c) and is ~2 % faster under the power cap
-    p.stages_used = a.K1 >= 24576 ? 4 : G2_STAGES;
+    // ring depth: 6 keeps the tensor pipe 95-99 % busy, but the deeper the ring the further the CTAs of a wave drift apart along K
+    // and the less they share each other's A / B panels in L2. ncu at M = 16384 (profiles/r02r_ring_depth.md): K = 14336 reads
+    // 3.49 GB per launch with 6 stages and 2.23 GB with 4 (and is 3 % faster), K = 28672 10.0 GB vs 4.47 GB (11 % faster); a
+    // 3-deep ring moves the same bytes as 4 but starves the tensor pipe (71 % active). 2.23 / 4.47 GB is 3.1-3.4x the
+    // algorithmic bytes: a wave of 74 256x256 tiles touches ~17 distinct 256-row panels of K columns each, and the panels of
+    // consecutive waves (8 x 7-15 MB of A, all of B) no longer fit the 126 MB L2 at these K.
+    p.stages_used = a.K1 >= 8192 ? 4 : G2_STAGES;
     if (SWIGLU == 1) p.stages_used = G2_STAGES - 1;      // the last ring stage is the third epilogue staging buffer
     p.lr_t = reinterpret_cast<const bf16*>(a.lr_t); p.lr_ldt = a.lr_ldt; p.lr_A = reinterpret_cast<const bf16*>(a.lr_A); p.lr_lda = a.lr_lda;
     for (int i = 0; i < 3; ++i) p.lr_bits[i] = reinterpret_cast<const unsigned long long*>(a.lr_bits[i]);

@@ -180,19 +180,32 @@ __global__ void __launch_bounds__(128, 4) dwconv3x3_kernel(const bf16* __restric
     }
 }
 
-// SE squeeze: mean over the HW positions of each frame. x [F, HW, C] -> out [F, C]; one thread per (f, 8 channels)
-__global__ void se_pool_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, long long F, int HW, int C) {
+// SE squeeze: mean over the HW positions of each frame. x [F, HW, C] -> out [F, C]. Block = 32 channel chunks x 8 position
+// slices: a warp reads 512 contiguous bytes per position, the 8 slices run in parallel and are summed in fixed order
+// (the one-thread-per-(f, chunk) version walked all HW positions serially with only F*C/8 threads in the grid).
+__global__ void __launch_bounds__(256) se_pool_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, long long F,
+                                                      int HW, int C) {
+    __shared__ float part[8][32][9];
     const int cpr = C / 8;
-    const long long total = F * cpr;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(i % cpr);
-        const long long f = i / cpr;
-        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        for (int p = 0; p < HW; ++p) {
+    const int c = blockIdx.x * 32 + threadIdx.x;
+    const long long f = blockIdx.y;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (c < cpr) {
+        for (int p = threadIdx.y; p < HW; p += 8) {
             float v[8];
             load8(x + (f * HW + p) * (long long)C + c * 8, v);
 #pragma unroll
             for (int j = 0; j < 8; ++j) acc[j] += v[j];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) part[threadIdx.y][threadIdx.x][j] = acc[j];
+    __syncthreads();
+    if (threadIdx.y == 0 && c < cpr) {
+#pragma unroll
+        for (int sl = 1; sl < 8; ++sl) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += part[sl][threadIdx.x][j];
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] /= (float)HW;
@@ -359,7 +372,9 @@ extern "C" int vlb_dwconv3x3(const void* x, const void* w9c, void* y, long long 
 
 extern "C" int vlb_se_pool(const void* x, void* out, long long F, int HW, int C, void* stream) {
     VLB_REQUIRE(C % 8 == 0, "se_pool: C=%d", C);
-    se_pool_kernel<<<grid_for(F * (C / 8), 64), 64, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)out, F, HW, C);
+    VLB_REQUIRE(F > 0 && F <= 65535 && HW > 0, "se_pool: F=%lld HW=%d", F, HW);
+    se_pool_kernel<<<dim3((unsigned)((C / 8 + 31) / 32), (unsigned)F), dim3(32, 8), 0, (cudaStream_t)stream>>>(
+        (const bf16*)x, (bf16*)out, F, HW, C);
     return check_launch("se_pool");
 }
 

@@ -179,3 +179,18 @@ def test_dwconv3x3_matches_torch_grouped_conv(F, Hh, Ww, C):
     err = (y.float() - ref).abs()
     tol = ref.abs() * 2.0 ** -7 + 1e-5          # one bf16 ulp of the result + fp32 reassociation noise
     assert bool((err <= tol).all()), float((err - tol).max())
+
+
+@pytest.mark.parametrize("F,HW,C", [(3, 576, 4096), (5, 169, 1024), (2, 1, 8), (2, 7, 264)])
+def test_se_pool_and_scale_match_fp32(F, HW, C):
+    """SE squeeze / excite of the STC RegStage bottleneck (timm SEModule: mean over H, W; x * gate) on NHWC rows."""
+    from phantom_vlb_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn(F * HW, C, device="cuda", generator=g).bfloat16()
+    pool = ops.se_pool(x, F, HW)
+    ref = x.float().view(F, HW, C).mean(1)
+    assert float((pool.float() - ref).abs().max()) <= float(ref.abs().max()) * 2.0 ** -7 + 1e-6
+    gate = torch.rand(F, C, device="cuda", generator=g).bfloat16()
+    y = ops.se_scale(x, gate, F, HW)
+    ref2 = (x.float().view(F, HW, C) * gate.float()[:, None, :]).reshape(F * HW, C)
+    assert float((y.float() - ref2).abs().max()) <= float(ref2.abs().max()) * 2.0 ** -7

@@ -4,8 +4,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from phantom_vlb_b200 import ops
 M = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
-for name, N, K, bmn in [("qkv", 6144, 4096, False), ("gu", 28672, 4096, False), ("d", 4096, 14336, False),
-                        ("d_gu", 4096, 28672, True), ("d_d", 14336, 4096, True)]:
+only = sys.argv[2].split(",") if len(sys.argv) > 2 else None
+for name, N, K, bmn in [s for s in [("qkv", 6144, 4096, False), ("gu", 28672, 4096, False), ("d", 4096, 14336, False),
+                        ("d_gu", 4096, 28672, True), ("d_d", 14336, 4096, True)] if only is None or s[0] in only]:
     a = torch.randn(M, K, device="cuda").bfloat16()
     w = (torch.randn((K, N) if bmn else (N, K), device="cuda") * 0.02).bfloat16()
     out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
