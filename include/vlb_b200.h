@@ -108,6 +108,20 @@ int vlb_hrf_pool_fwd(const void* x, const void* norm_w, const void* ln1_w, const
 int vlb_hrf_pool_finalize(const void* partial_f32, const void* ln2_w, const void* ln2_b, void* pooled,
                           void* hrf, void* keep_scale_f32, int B, int H, int nch, float eps, float drop_p,
                           unsigned long long seed, void* stream);
+/* vlb_hrf_pool_fwd followed by vlb_hrf_pool_finalize in ONE call that allocates nothing, for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). NO COUNTERPART IN THE REFERENCE.
+ * The partial[B, nch, H] scratch between the two kernels lives in a file-scope
+ * `static __device__` array of the library (2 MiB on every GPU that loads it, held until the process exits); its device
+ * address is resolved once per device with cudaGetSymbolAddress. Limit: B * nch * H <= vlb_hrf_pool_static_max_floats()
+ * (= 524 288 floats; e.g. B=8, H=4096, nch<=16) -- larger requests return non-zero with a message, nothing is launched.
+ * Same arguments, meaning and results as the two-call form (eps_ln is used for both LayerNorms, as the engine does).
+ * Every call on a device shares the array: calls that overlap on the GPU (different streams without a dependency) RACE;
+ * calls on one stream are safe. Nothing needs clearing between calls: the first kernel overwrites all it later reads. */
+int vlb_hrf_pool_static_max_floats(void);
+int vlb_hrf_pool_fwd_static(const void* x, const void* norm_w, const void* ln1_w, const void* ln1_b,
+                            const void* wmask_f32, const void* ln2_w, const void* ln2_b, void* pooled, void* hrf,
+                            void* keep_scale_f32, int B, int S, int H, int nch, float eps_rms, float eps_ln,
+                            float drop_p, unsigned long long seed, void* stream);
 /* HRFConvolveLayer as a stand-alone layer (src/utils.py:40-56, exported by src/__init__.py:3-13):
  * out_f32[b, e] = sum_s w_f32[b, s] * emb[b, s, e]  (emb bf16 [B, S, H], fp32 accumulate; out is zeroed inside).
  * Backward of the same einsum: demb[b, s, :] = w[b, s] * dout[b, :] (bf16, nullable), dw_f32[b, s] = <emb[b, s, :], dout[b, :]>

@@ -6,6 +6,7 @@
 // (system prompt, instruction, padding: ~60 % of the 2048 tokens) are never fetched in the forward pass.
 // Rounding points mirror bf16 autocast: LN outputs fp32 -> einsum operands bf16 -> pooled bf16 -> LN2 fp32 -> bf16.
 #include "common.cuh"
+#include <mutex>
 
 namespace vlb {
 
@@ -629,4 +630,66 @@ extern "C" int vlb_head_gradnorm(const void* dpred, const void* pred, const void
         (const bf16*)dpred, (const bf16*)pred, (const bf16*)bias, (const float*)gram_dpred_f32, (const float*)gram_hrf_f32,
         (const float*)wsq_f32, (float*)sumsq_f32, N, ld_gram, P, l2_lambda);
     return check_launch("head_gradnorm");
+}
+
+// ------------------------------------------------------------------ pooled head forward with NO allocation anywhere
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
+// vlb_hrf_pool_fwd + vlb_hrf_pool_finalize in one call, with the partial[B, nch, H] scratch between them in a file-scope
+// device array instead of a caller buffer. The array is part of the library image: every GPU that loads libvlb_b200 holds
+// these 2 MiB until the process exits. All calls on a device share it, so two calls that overlap on the GPU (different
+// streams, no dependency) race; calls on one stream are ordered and safe. Nothing has to start at zero: the pooling kernel
+// overwrites every element of partial[0 : B*nch*H) that the finalize kernel of the same call reads.
+constexpr long long POOL_STATIC_MAX_FLOATS = 512 * 1024;           // B * nch * H <= 524 288 floats (2 MiB)
+static __device__ __align__(256) float g_pool_static_scratch[POOL_STATIC_MAX_FLOATS];
+
+namespace {
+constexpr int POOL_STATIC_MAX_DEVICES = 64;
+float* g_pool_static_ptr[POOL_STATIC_MAX_DEVICES];                 // device address of the array, per device ordinal
+std::mutex g_pool_static_mu;
+
+// In host code `g_pool_static_scratch` is only a handle of the symbol, not a device address: resolve it once per device,
+// with that device current, and hand the kernels the resolved pointer.
+int pool_static_scratch(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { set_error("hrf_pool_fwd_static: cudaGetDevice: %s", cudaGetErrorString(e)); return (int)e; }
+    if (dev < 0 || dev >= POOL_STATIC_MAX_DEVICES) { set_error("hrf_pool_fwd_static: device ordinal %d out of range", dev); return 1; }
+    std::lock_guard<std::mutex> lk(g_pool_static_mu);
+    if (!g_pool_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_pool_static_scratch);
+        if (e != cudaSuccess || !p) {
+            set_error("hrf_pool_fwd_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : 1;
+        }
+        g_pool_static_ptr[dev] = (float*)p;
+    }
+    *out = g_pool_static_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" int vlb_hrf_pool_static_max_floats(void) { return (int)POOL_STATIC_MAX_FLOATS; }
+
+extern "C" int vlb_hrf_pool_fwd_static(const void* x, const void* norm_w, const void* ln1_w, const void* ln1_b,
+                                       const void* wmask_f32, const void* ln2_w, const void* ln2_b, void* pooled,
+                                       void* hrf, void* keep_scale_f32, int B, int S, int H, int nch, float eps_rms,
+                                       float eps_ln, float drop_p, unsigned long long seed, void* stream) {
+    VLB_REQUIRE(B > 0 && S > 0 && H % 8 == 0 && H > 0 && H <= 8 * HT * HV && nch > 0 && nch <= S,
+                "hrf_pool_fwd_static: B=%d S=%d H=%d nch=%d", B, S, H, nch);
+    const long long need = (long long)B * nch * H;
+    VLB_REQUIRE(need <= POOL_STATIC_MAX_FLOATS,
+                "hrf_pool_fwd_static: B*nch*H = %lld floats exceeds the built-in scratch of %lld floats (2 MiB); lower nch or "
+                "use vlb_hrf_pool_fwd + vlb_hrf_pool_finalize with a caller buffer", need, POOL_STATIC_MAX_FLOATS);
+    float* partial = nullptr;
+    if (int rc = pool_static_scratch(&partial)) return rc;
+    const int rows_per = ceil_div(S, nch);
+    hrf_pool_fwd_kernel<<<dim3(nch, B), HT, 0, (cudaStream_t)stream>>>(
+        (const bf16*)x, (const bf16*)norm_w, (const bf16*)ln1_w, (const bf16*)ln1_b, (const float*)wmask_f32, partial, S, H,
+        rows_per, eps_rms, eps_ln);
+    if (int rc = check_launch("hrf_pool_fwd_static/pool")) return rc;
+    hrf_pool_finalize_kernel<<<B, HT, 0, (cudaStream_t)stream>>>(partial, (const bf16*)ln2_w, (const bf16*)ln2_b,
+                                                                (bf16*)pooled, (bf16*)hrf, (float*)keep_scale_f32, nch, H,
+                                                                eps_ln, drop_p, seed);
+    return check_launch("hrf_pool_fwd_static/finalize");
 }
