@@ -174,6 +174,25 @@ __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
 __device__ __forceinline__ void sts128(uint32_t saddr, const uint4& v) {
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+__device__ __forceinline__ void lds64(uint32_t saddr, uint32_t& a, uint32_t& b) {
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(saddr) : "memory");
+}
+__device__ __forceinline__ uint4 lds128_sync(uint32_t saddr) {      // ordered against other shared-memory traffic (hand-offs)
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t saddr, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" :: "r"(saddr), "r"(v) : "memory");
+}
+// warp-level bf16 MMA (m16n8k16, fp32 accumulate from zero) for rank-16 side products inside epilogues: runs on the legacy
+// tensor-core path next to the tcgen05 main loop. Fragments: a0..a3 = rows (g, g+8) x k (2c, 2c+8) pairs, b0/b1 = k (2c, 2c+8)
+// pairs of column g, d0..d3 = rows (g, g+8) x columns (2c, 2c+1), with g = lane / 4, c = lane % 4.
+__device__ __forceinline__ void mma16816_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.f));
+}
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }

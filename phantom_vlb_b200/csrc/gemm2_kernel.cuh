@@ -36,22 +36,32 @@ constexpr int G2_TMEM_COLS = 512;
 template <int SWIGLU, bool LORA = false> __host__ __device__ constexpr int g2_threads() { return (SWIGLU == 0 || (SWIGLU == 2 && LORA)) ? 384 : 256; }
 
 // LORA_EPI (dX GEMMs under LoRA dropout): the adapter branch of the input gradient, 1/(1-p) * keep_a . (t_a A_a), cannot ride in
-// the accumulator as a k-block (the keep mask sits between the rank-16 product and the sum), so the epilogue forms it on the
-// CUDA cores: A_a's 256 columns of the tile are staged in the ring stage this mode leaves unused (5-deep ring), every thread
-// holds its row of t in registers, and per 8 columns 16 broadcast LDS.128 + 128 FMA per adapter run in the shadow of the next
-// tile's main loop. v[i] += scale * keep_i * sum_j t[j] A[j][col + i]
-__device__ __forceinline__ void lora_rank16_add8(float (&v)[8], const float* t, uint32_t a_col, int row_bytes,
+// the accumulator as a k-block (the keep mask sits between the rank-16 product and the sum), so the epilogue forms it beside the
+// tcgen05 main loop with warp-level MMAs: per 8 columns and adapter a warp computes P[32 rows, 8] = T_a[32, 16] A_a[16, 8] with
+// two mma.sync m16n8k16 (T fragments in registers for the whole tile, the B fragment one conflict-free LDS.64 from A_a's columns
+// staged in the ring stage this mode leaves unused), hands P from the MMA fragment layout to one-row-per-lane (the TMEM layout)
+// through a 512-byte warp-private buffer, and adds the kept elements. An earlier version did the product on the CUDA cores from
+// broadcast LDS.128 (16 loads = 64 shared-memory wavefronts + 256 issue slots per 8 columns and adapter): with the main loop
+// already using ~3/4 of the shared-memory bandwidth (TMA writes + operand reads) that epilogue slowed the MMAs down.
+//   v[i] += scale * keep_i * sum_j t[j] A[j][col + i]
+constexpr int LA_REC_BYTES = 32;                          // one column of one adapter: 16 bf16 in B-fragment order
+constexpr int LA_XBUF_BYTES = 1024;                       // per warp: two 32 x 16 B hand-off buffers
+__device__ __forceinline__ void lora_rank16_add8(float (&v)[8], const uint32_t (&tf)[8], uint32_t brec, uint32_t xbuf, int lane,
                                                  unsigned int byte, float scale) {
+    uint32_t b0, b1;
+    lds64(brec, b0, b1);
+    const uint32_t ta[4] = {tf[0], tf[1], tf[2], tf[3]}, tb[4] = {tf[4], tf[5], tf[6], tf[7]};
+    float d0[4], d1[4];
+    mma16816_bf16(d0, ta, b0, b1);                        // rows g, g + 8 of the warp's 32
+    mma16816_bf16(d1, tb, b0, b1);                        // rows 16 + g, 24 + g
+    const uint32_t w = xbuf + (uint32_t)(lane >> 2) * 16 + (uint32_t)(lane & 3) * 4;
+    sts32(w, pack_bf16(d0[0], d0[1]));
+    sts32(w + 8 * 16, pack_bf16(d0[2], d0[3]));
+    sts32(w + 16 * 16, pack_bf16(d1[0], d1[1]));
+    sts32(w + 24 * 16, pack_bf16(d1[2], d1[3]));
+    __syncwarp();
     float acc[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-        float f[8];
-        unpack8(lds128(a_col + j * row_bytes), f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] = fmaf(t[j], f[i], acc[i]);
-    }
+    unpack8(lds128_sync(xbuf + (uint32_t)lane * 16), acc);
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] += ((byte >> i) & 1u) ? acc[i] * scale : 0.f;
 }
@@ -181,41 +191,58 @@ gemm2_tcgen05_kernel(const GemmParams p,
             }
             const int m = m0 + row;
             const bool m_ok = m < p.M;
-            float lt[LORA ? 48 : 1];                        // this row of t (rank-16 coefficients of up to three adapters)
+            constexpr int LA_COLS = G2_BN / 2;                           // tile columns one epilogue warpgroup owns
+            constexpr int LA_AD_BYTES = LA_COLS * LA_REC_BYTES;          // 4 KB per adapter and warpgroup
+            uint32_t tf[LORA ? 3 : 1][8];                   // mma.sync A fragments of this warp's 32 rows of t, per adapter
             uint32_t la = 0;                                // this warpgroup's staged columns of A (shared-space address)
-            constexpr int LA_ROW_BYTES = (G2_BN / 2) * 2;  // each warpgroup stages the 128 columns it owns
+            uint32_t xb = 0;                                // this warp's hand-off buffers
+            uint32_t xsel = 0;
             if constexpr (LORA) {
                 // every thread of the warpgroup is past the last bar.sync of its previous tile, so nobody still reads the old A.
                 // plain variant: ring stage 5 is free (5-deep ring); SwiGLU variant: stages 4 and 5 are free (4-deep ring), the A
-                // slots of those hold the second warpgroup's output staging buffers, the B slot of stage 4 the two A regions
+                // slots of those hold the second warpgroup's output staging buffers, the B slot of stage 4 the two A regions.
+                // Region of a warpgroup: [adapter][column of its 128][32 B record] then 4 x 1 KB hand-off buffers.
                 uint8_t* law = SWIGLU == 2 ? smem_b + (STAGES - 2) * G2_B_BYTES + wg * (G2_B_BYTES / 2)
                                            : (wg == 0 ? smem_a : smem_b) + (STAGES - 1) * G2_A_BYTES;
-                constexpr int CHUNKS_PER_ROW = LA_ROW_BYTES / 16;
-                const int tid = q * 32 + lane;
-                const int ncol0 = n0 + wg * (G2_BN / 2);
-                for (int idx = tid; idx < 16 * p.lr_na * CHUNKS_PER_ROW; idx += 128) {
-                    const int rj = idx / CHUNKS_PER_ROW, c16 = idx - rj * CHUNKS_PER_ROW;
-                    const int ncol = ncol0 + c16 * 8;
-                    uint4 val = make_uint4(0u, 0u, 0u, 0u);
-                    if (ncol < p.N) val = __ldg(reinterpret_cast<const uint4*>(p.lr_A + (size_t)rj * p.lr_lda + ncol));
-                    sts128(smem_u32(law) + rj * LA_ROW_BYTES + c16 * 16, val);
-                }
                 la = smem_u32(law);
+                xb = la + (SWIGLU == 2 ? 1 : 3) * LA_AD_BYTES + q * LA_XBUF_BYTES;
+                const unsigned short* Ag = reinterpret_cast<const unsigned short*>(p.lr_A);
+                for (int idx = q * 32 + lane; idx < p.lr_na * LA_COLS; idx += 128) {      // one column of one adapter per thread
+                    const int a = idx / LA_COLS, tid = idx - a * LA_COLS;
+                    const int ncol = n0 + wg * LA_COLS + tid;
+                    uint32_t rec[8];
 #pragma unroll
-                for (int c = 0; c < 6; ++c) {
-                    uint4 tv = make_uint4(0u, 0u, 0u, 0u);
-                    if (m_ok && c * 8 < 16 * p.lr_na) tv = __ldg(reinterpret_cast<const uint4*>(p.lr_t + (size_t)m * p.lr_ldt + c * 8));
-                    float f[8]; unpack8(tv, f);
+                    for (int c = 0; c < 4; ++c) {           // record order: k = 2c, 2c+1, 2c+8, 2c+9
+                        uint32_t kv[4];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) lt[c * 8 + j] = f[j];
+                        for (int e = 0; e < 4; ++e) {
+                            const int k = 2 * c + (e & 1) + (e >> 1) * 8;
+                            kv[e] = ncol < p.N ? (uint32_t)__ldg(Ag + (size_t)(a * 16 + k) * p.lr_lda + ncol) : 0u;
+                        }
+                        rec[2 * c] = kv[0] | (kv[1] << 16);
+                        rec[2 * c + 1] = kv[2] | (kv[3] << 16);
+                    }
+                    const uint32_t dst = la + a * LA_AD_BYTES + tid * LA_REC_BYTES;
+                    sts128(dst, make_uint4(rec[0], rec[1], rec[2], rec[3]));
+                    sts128(dst + 16, make_uint4(rec[4], rec[5], rec[6], rec[7]));
                 }
+                const int g = lane >> 2, c2 = (lane & 3) * 2;
+                const uint32_t* tg = reinterpret_cast<const uint32_t*>(p.lr_t);
+#pragma unroll
+                for (int a = 0; a < 3; ++a)
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {           // e = 4 h + 2 (k half) + (row half)
+                        const int r = m0 + q * 32 + (e >> 2) * 16 + g + (e & 1) * 8;
+                        const int k = a * 16 + c2 + ((e >> 1) & 1) * 8;
+                        tf[a][e] = (a < p.lr_na && r < p.M) ? __ldg(tg + ((size_t)r * p.lr_ldt + k) / 2) : 0u;
+                    }
             }
             mbar_wait(&tfull_bar[as], aphase);
             tc_fence_after();
             if constexpr (SWIGLU == 2 && LORA) {
                 // Two warpgroups (384 threads), each owning 128 of the tile's 256 columns with its own pair of staging buffers:
-                // with four warps the adapter term (16 LDS.128 + 128 FMA per 8 columns) on top of the SwiGLU backward made the
-                // epilogue longer than the K = 4096 main loop. Rolled over 8-column chunks: unrolled, this code overflowed the
+                // with four warps (one per scheduler, latency-bound) the SwiGLU backward plus the adapter term made the epilogue
+                // longer than the K = 4096 main loop (ncu: tensor pipe 54 % active, against 86 % for the variant without adapters). Rolled over 8-column chunks: unrolled, this code overflowed the
                 // instruction cache and the warps stalled on instruction fetch.
                 uint8_t* cdg = wg == 0 ? smem_cd : smem_a + (STAGES - 2) * G2_A_BYTES;
                 uint8_t* cdu = cdg + CD_STAGE_BYTES;
@@ -249,7 +276,9 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         unpack8(gv, g); unpack8(uv, u);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r8[j]) * p.alpha;
-                        lora_rank16_add8(dv, lt, la + (sl * 64 + ch * 8) * 2, LA_ROW_BYTES, (unsigned int)(kw >> (ch * 8)) & 0xFFu, p.lr_scale);
+                        lora_rank16_add8(dv, tf[0], la + (sl * 64 + ch * 8 + (lane >> 2)) * LA_REC_BYTES + (lane & 3) * 8, xb + xsel, lane,
+                                         (unsigned int)(kw >> (ch * 8)) & 0xFFu, p.lr_scale);
+                        xsel ^= 512u;
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const float d = bf2f(f2bf(dv[j]));
@@ -310,9 +339,6 @@ gemm2_tcgen05_kernel(const GemmParams p,
                             unpack8(gv[c], g); unpack8(uv[c], u);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
-                            if constexpr (LORA)
-                                lora_rank16_add8(dv, lt, la + (c0 + c * 8) * 2, LA_ROW_BYTES,
-                                                 (unsigned int)(kw >> (h * 32 + c * 8)) & 0xFFu, p.lr_scale);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) {
                                 const float d = bf2f(f2bf(dv[j]));                                     // d(act) as the unfused path stores it
@@ -418,9 +444,11 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r8[j]) * p.alpha;
 #pragma unroll
                         for (int a = 0; a < 3; ++a)
-                            if (a < p.lr_na)
-                                lora_rank16_add8(v, lt + a * 16, la + a * 16 * LA_ROW_BYTES + (sl * 64 + ch * 8) * 2, LA_ROW_BYTES,
-                                                 (unsigned int)(kw[a] >> (ch * 8)) & 0xFFu, p.lr_scale);
+                            if (a < p.lr_na) {
+                                lora_rank16_add8(v, tf[a], la + a * LA_AD_BYTES + (sl * 64 + ch * 8 + (lane >> 2)) * LA_REC_BYTES + (lane & 3) * 8,
+                                                 xb + xsel, lane, (unsigned int)(kw[a] >> (ch * 8)) & 0xFFu, p.lr_scale);
+                                xsel ^= 512u;
+                            }
                         uint4 u;
                         u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);
                         u.z = pack_bf16(v[4], v[5]); u.w = pack_bf16(v[6], v[7]);
@@ -479,9 +507,11 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         if constexpr (LORA) {
 #pragma unroll
                             for (int a = 0; a < 3; ++a)
-                                if (a < p.lr_na)
-                                    lora_rank16_add8(v, lt + a * 16, la + a * 16 * LA_ROW_BYTES + (sl * 64 + h * 32 + c * 8) * 2,
-                                                     LA_ROW_BYTES, (unsigned int)(kw[a] >> (h * 32 + c * 8)) & 0xFFu, p.lr_scale);
+                                if (a < p.lr_na) {      // (not reached: the LORA instantiations leave through the rolled loop above)
+                                    lora_rank16_add8(v, tf[a], la + a * LA_AD_BYTES + (sl * 64 + h * 32 + c * 8 + (lane >> 2)) * LA_REC_BYTES + (lane & 3) * 8,
+                                                     xb + xsel, lane, (unsigned int)(kw[a] >> (h * 32 + c * 8)) & 0xFFu, p.lr_scale);
+                                    xsel ^= 512u;
+                                }
                         }
                         if (has_bias) {
                             float b[8]; unpack8(bv[c], b);

@@ -15,16 +15,36 @@ constexpr int HV = 4;         // 8-element chunks per thread (H <= 8*HT*HV = 409
 
 struct RowStats { float rstd_rms, mean1, rstd1; };
 
-// loads row x, applies RMSNorm (bf16 rounding as MistralRMSNorm) -> z, then LN1 statistics over z.
-__device__ __forceinline__ RowStats row_norms(const bf16* __restrict__ xr, const bf16* __restrict__ wn, int H,
-                                              float eps_rms, float eps_ln, float (&z)[HV][8], float* red) {
+// this thread's 16-byte chunks of one row, still packed (issued early so that the next row is in flight during the reductions)
+__device__ __forceinline__ void load_row_raw(const bf16* __restrict__ xr, int nchunk, uint4 (&raw)[HV]) {
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+        const int c = threadIdx.x + i * HT;
+        raw[i] = c < nchunk ? __ldg(reinterpret_cast<const uint4*>(xr) + c) : make_uint4(0, 0, 0, 0);
+    }
+}
+
+// first live (weight != 0) row at or after r in the CTA's staged weights
+__device__ __forceinline__ int next_live(const float* wsm, int r, int n) {
+    while (r < n && wsm[r] == 0.f) ++r;
+    return r;
+}
+
+__device__ __forceinline__ void unpack_row(const uint4 (&raw)[HV], int nchunk, float (&z)[HV][8]) {
+#pragma unroll
+    for (int i = 0; i < HV; ++i)
+        if (threadIdx.x + i * HT < nchunk) unpack8(raw[i], z[i]);
+}
+
+// z holds the row on entry: RMSNorm (bf16 rounding as MistralRMSNorm) -> z, then LN1 statistics over z.
+__device__ __forceinline__ RowStats row_norms_z(float (&z)[HV][8], const bf16* __restrict__ wn, int H,
+                                                float eps_rms, float eps_ln, float* red) {
     const int nchunk = H / 8;
     float ss = 0.f;
 #pragma unroll
     for (int i = 0; i < HV; ++i) {
         const int c = threadIdx.x + i * HT;
         if (c < nchunk) {
-            load8(xr + c * 8, z[i]);
 #pragma unroll
             for (int j = 0; j < 8; ++j) ss += z[i][j] * z[i][j];
         }
@@ -55,12 +75,25 @@ __device__ __forceinline__ RowStats row_norms(const bf16* __restrict__ xr, const
     return st;
 }
 
+// loads row x, applies RMSNorm -> z, then LN1 statistics over z.
+__device__ __forceinline__ RowStats row_norms(const bf16* __restrict__ xr, const bf16* __restrict__ wn, int H,
+                                              float eps_rms, float eps_ln, float (&z)[HV][8], float* red) {
+    uint4 raw[HV];
+    load_row_raw(xr, H / 8, raw);
+    unpack_row(raw, H / 8, z);
+    return row_norms_z(z, wn, H, eps_rms, eps_ln, red);
+}
+
 // grid (nch, B): CTA accumulates sum_s w[b,s] * bf16(LN1(RMSNorm(x[b,s]))) over its slice of rows -> partial[b, ch, :]
+// The CTA's HRF weights are staged in shared memory once (one coalesced load instead of a dependent global load per row) and the
+// next live row is fetched before the three block reductions of the current one: the kernel is latency-bound (a few live rows
+// per CTA, each a load -> reduce -> reduce -> reduce chain), not bandwidth-bound.
 __global__ void __launch_bounds__(HT) hrf_pool_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ wn,
                                                           const bf16* __restrict__ g1, const bf16* __restrict__ b1,
                                                           const float* __restrict__ wmask, float* __restrict__ partial,
                                                           int S, int H, int rows_per, float eps_rms, float eps_ln) {
     __shared__ float red[32];
+    __shared__ float wsm[HT];
     const int b = blockIdx.y, ch = blockIdx.x, nch = gridDim.x;
     const int nchunk = H / 8;
     float acc[HV][8];
@@ -69,20 +102,32 @@ __global__ void __launch_bounds__(HT) hrf_pool_fwd_kernel(const bf16* __restrict
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
     const int s0 = ch * rows_per, s1 = min(S, s0 + rows_per);
-    for (int s = s0; s < s1; ++s) {
-        const float wgt = wmask[(size_t)b * S + s];
-        if (wgt == 0.f) continue;                                  // uniform across the CTA
-        float z[HV][8];
-        const RowStats st = row_norms(x + ((size_t)b * S + s) * H, wn, H, eps_rms, eps_ln, z, red);
+    for (int base = s0; base < s1; base += HT) {
+        const int n = min(HT, s1 - base);
+        __syncthreads();                                           // the previous batch of weights is no longer read
+        if (threadIdx.x < n) wsm[threadIdx.x] = wmask[(size_t)b * S + base + threadIdx.x];
+        __syncthreads();
+        const bf16* xb = x + ((size_t)b * S + base) * H;
+        int r = next_live(wsm, 0, n);                              // uniform across the CTA
+        uint4 raw[HV];
+        if (r < n) load_row_raw(xb + (size_t)r * H, nchunk, raw);
+        while (r < n) {
+            const float wgt = wsm[r];
+            float z[HV][8];
+            unpack_row(raw, nchunk, z);
+            r = next_live(wsm, r + 1, n);
+            if (r < n) load_row_raw(xb + (size_t)r * H, nchunk, raw);                  // in flight during the reductions below
+            const RowStats st = row_norms_z(z, wn, H, eps_rms, eps_ln, red);
 #pragma unroll
-        for (int i = 0; i < HV; ++i) {
-            const int c = threadIdx.x + i * HT;
-            if (c < nchunk) {
-                float g[8], bb[8];
-                load8(g1 + c * 8, g); load8(b1 + c * 8, bb);
+            for (int i = 0; i < HV; ++i) {
+                const int c = threadIdx.x + i * HT;
+                if (c < nchunk) {
+                    float g[8], bb[8];
+                    load8(g1 + c * 8, g); load8(b1 + c * 8, bb);
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    acc[i][j] += wgt * bf2f(f2bf((z[i][j] - st.mean1) * st.rstd1 * g[j] + bb[j]));
+                    for (int j = 0; j < 8; ++j)
+                        acc[i][j] += wgt * bf2f(f2bf((z[i][j] - st.mean1) * st.rstd1 * g[j] + bb[j]));
+                }
             }
         }
     }
@@ -118,7 +163,8 @@ __global__ void __launch_bounds__(HT) hrf_pool_finalize_kernel(const float* __re
         if (c < nchunk) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
-            for (int k = 0; k < nch; ++k) {
+#pragma unroll 8
+            for (int k = 0; k < nch; ++k) {                       // fixed summation order; the loads are independent
                 float t[8]; load8(partial + ((size_t)b * nch + k) * H + c * 8, t);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) v[i][j] += t[j];
@@ -271,6 +317,11 @@ __global__ void __launch_bounds__(HT) ln2_bwd_kernel(const float* __restrict__ d
     }
 }
 
+// fire-and-forget 16-byte fp32 reduction (sm_90+)
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // Backward of pooling + LN1 + final RMSNorm. grid (nch, B). For each row: dx = 0 if w == 0, else
 //   gu = w * bf16?(dpooled)   (grad wrt LN1 output), LN1 backward -> gz, RMSNorm backward -> dx (bf16).
 // dg1/db1 accumulate per CTA in registers and are flushed with one atomicAdd per element.
@@ -360,13 +411,15 @@ __global__ void __launch_bounds__(HT) hrf_pool_bwd_kernel(const bf16* __restrict
             }
         }
     }
-    if (any) {
+    if (any) {                                 // 512 CTAs add into the same 2 x H floats: 16-byte reductions, a quarter of the operations
 #pragma unroll
         for (int i = 0; i < HV; ++i) {
             const int c = threadIdx.x + i * HT;
             if (c < nchunk) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) { atomicAdd(dg1 + c * 8 + j, ag[i][j]); atomicAdd(db1 + c * 8 + j, ab[i][j]); }
+                red_add_v4(dg1 + c * 8, ag[i][0], ag[i][1], ag[i][2], ag[i][3]);
+                red_add_v4(dg1 + c * 8 + 4, ag[i][4], ag[i][5], ag[i][6], ag[i][7]);
+                red_add_v4(db1 + c * 8, ab[i][0], ab[i][1], ab[i][2], ab[i][3]);
+                red_add_v4(db1 + c * 8 + 4, ab[i][4], ab[i][5], ab[i][6], ab[i][7]);
             }
         }
     }

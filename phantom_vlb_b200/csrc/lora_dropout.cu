@@ -34,24 +34,42 @@ __device__ __forceinline__ unsigned int hash32(unsigned int x, unsigned int k1, 
     return x ^ (x >> 16);
 }
 
-// One thread per 64-bit word. keep_i = (u_i >= thresh) for 64 independent 32-bit uniforms u_i, evaluated bit-serially from the
-// most significant bit: random word number b holds bit (31 - b) of all 64 uniforms at once, a lane is decided as soon as its
-// bit differs from thresh's, and the loop ends when every lane is decided -- about 8 words instead of 64 hashes per word, with
-// the drop probability still exactly thresh / 2^32.
-__global__ void __launch_bounds__(256) dropout_bits_kernel(unsigned long long* __restrict__ bits, long long nwords,
-                                                           unsigned int thresh, unsigned long long seed) {
+// One thread per 64-bit word. keep_i = (u_i >= thresh) for 64 independent 32-bit uniforms u_i. The top DB_PLANES bits are
+// evaluated bit-serially for all 64 lanes at once (random word number b holds bit (31 - b) of all 64 uniforms; a lane is
+// decided as soon as its bit differs from thresh's), which leaves 64 / 2^DB_PLANES = 1 lane per word undecided on average;
+// those draw their remaining 32 - DB_PLANES bits from one more hash each. The drop probability is exactly thresh / 2^32.
+// (Running the planes until the whole warp is decided costs the MAXIMUM over 2048 lanes, ~12 planes; this costs 6 + a tail.)
+// 128 threads x 18 registers per block: small enough to sit beside a 384-thread pair-GEMM CTA on the same SM, so the masks of
+// a step can be generated on a side stream underneath the tensor-core kernels (Engine._pregen_masks).
+constexpr int DB_PLANES = 6;
+constexpr int DB_THREADS = 128;
+__global__ void __launch_bounds__(DB_THREADS) dropout_bits_kernel(unsigned long long* __restrict__ bits, long long nwords,
+                                                                  unsigned int thresh, unsigned long long seed) {
     const long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (w >= nwords) return;
     const unsigned long long key = mix64(seed ^ 0xD1B54A32D192ED03ull);
     const unsigned int k1 = (unsigned int)key ^ (unsigned int)((unsigned long long)w >> 26) * 0x9E3779B1u, k2 = (unsigned int)(key >> 32);
-    const unsigned int ctr = (unsigned int)w << 6;                 // 64 counters per word: 32 bit positions x 2 halves
+    const unsigned int ctr = (unsigned int)w << 6;                 // 64 counters per word
     unsigned int keep0 = 0, keep1 = 0, und0 = 0xFFFFFFFFu, und1 = 0xFFFFFFFFu;
-    for (int b = 0; b < 32 && (und0 | und1); ++b) {
+#pragma unroll
+    for (int b = 0; b < DB_PLANES; ++b) {
         const unsigned int r0 = hash32(ctr + 2 * b, k1, k2), r1 = hash32(ctr + 2 * b + 1, k1, k2);
         if ((thresh >> (31 - b)) & 1u) { und0 &= r0; und1 &= r1; }                      // uniform bit 0 under a 1: below thresh, dropped
         else { keep0 |= und0 & r0; keep1 |= und1 & r1; und0 &= ~r0; und1 &= ~r1; }      // uniform bit 1 over a 0: above thresh, kept
     }
-    bits[w] = (unsigned long long)(keep0 | und0) | ((unsigned long long)(keep1 | und1) << 32);     // all 32 bits equal: u == thresh, kept
+    // lanes whose top DB_PLANES bits equal thresh's: compare the remaining bits, drawn per lane from a second key stream
+    const unsigned int tl = thresh & (0xFFFFFFFFu >> DB_PLANES), k3 = k1 ^ 0xA511E9B3u;
+    while (und0) {
+        const int i = __ffs(und0) - 1;
+        und0 &= und0 - 1;
+        if ((hash32(ctr + i, k3, k2) >> DB_PLANES) >= tl) keep0 |= 1u << i;
+    }
+    while (und1) {
+        const int i = __ffs(und1) - 1;
+        und1 &= und1 - 1;
+        if ((hash32(ctr + 32 + i, k3, k2) >> DB_PLANES) >= tl) keep1 |= 1u << i;
+    }
+    bits[w] = (unsigned long long)keep0 | ((unsigned long long)keep1 << 32);
 }
 
 constexpr int LM_BM = 128;            // MMA M: tokens (forward) / features (backward)
@@ -312,7 +330,7 @@ extern "C" int vlb_dropout_bits(void* bits64, long long n_tok, int n_feat, float
     const long long nwords = n_tok * (n_feat / 64);
     double th = (double)p * 4294967296.0 + 0.5;
     const unsigned int thresh = th >= 4294967295.0 ? 4294967295u : (unsigned int)th;
-    dropout_bits_kernel<<<(unsigned)ceil_div_ll(nwords, 256), 256, 0, (cudaStream_t)stream>>>((unsigned long long*)bits64, nwords,
+    dropout_bits_kernel<<<(unsigned)ceil_div_ll(nwords, DB_THREADS), DB_THREADS, 0, (cudaStream_t)stream>>>((unsigned long long*)bits64, nwords,
                                                                                                 thresh, seed);
     return check_launch("dropout_bits");
 }

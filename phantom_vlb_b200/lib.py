@@ -6,7 +6,7 @@ import os
 import re
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvlb_b200.so")
+LIB_PATH = os.environ.get("VLB_LIB_PATH") or os.path.join(HERE, "libvlb_b200.so")     # override: A/B builds during tuning
 HEADER = os.path.join(os.path.dirname(HERE), "include", "vlb_b200.h")
 
 _CTYPES = {
