@@ -182,6 +182,11 @@ __device__ __forceinline__ uint4 lds128_sync(uint32_t saddr) {      // ordered a
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr) : "memory");
     return v;
 }
+__device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
+    return v;
+}
 __device__ __forceinline__ void sts32(uint32_t saddr, uint32_t v) {
     asm volatile("st.shared.u32 [%0], %1;" :: "r"(saddr), "r"(v) : "memory");
 }

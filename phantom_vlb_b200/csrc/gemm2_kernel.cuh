@@ -66,6 +66,36 @@ __device__ __forceinline__ void lora_rank16_add8(float (&v)[8], const uint32_t (
     for (int i = 0; i < 8; ++i) v[i] += ((byte >> i) & 1u) ? acc[i] * scale : 0.f;
 }
 
+// Same product with the B fragment already in registers and the hand-off through the 16-byte slots of the output staging buffer
+// that this chunk's results are about to overwrite anyway (row r, chunk ch -> r * 128 + ((ch ^ (r & 7)) << 4), the 128B-swizzle
+// pattern): no shared memory of its own, which is what lets the SwiGLU-backward variant keep a 5-deep ring.
+__device__ __forceinline__ void lora_rank16_add8_slots(float (&v)[8], const uint32_t (&tf)[8], uint32_t b0, uint32_t b1, uint32_t cd,
+                                                       int q, int lane, int ch, unsigned int byte, float scale) {
+    const uint32_t ta[4] = {tf[0], tf[1], tf[2], tf[3]}, tb[4] = {tf[4], tf[5], tf[6], tf[7]};
+    float d0[4], d1[4];
+    mma16816_bf16(d0, ta, b0, b1);
+    mma16816_bf16(d1, tb, b0, b1);
+    const int g = lane >> 2;
+    const uint32_t w = cd + (uint32_t)(q * 32 + g) * 128 + (uint32_t)((ch ^ g) << 4) + (uint32_t)(lane & 3) * 4;   // (row & 7) == g for all four rows
+    sts32(w, pack_bf16(d0[0], d0[1]));
+    sts32(w + 8 * 128, pack_bf16(d0[2], d0[3]));
+    sts32(w + 16 * 128, pack_bf16(d1[0], d1[1]));
+    sts32(w + 24 * 128, pack_bf16(d1[2], d1[3]));
+    __syncwarp();
+    const int row = q * 32 + lane;
+    float acc[8];
+    unpack8(lds128_sync(cd + (uint32_t)row * 128 + (uint32_t)((ch ^ (row & 7)) << 4)), acc);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] += ((byte >> i) & 1u) ? acc[i] * scale : 0.f;
+}
+
+// B fragment (k = 2c, 2c+1 | 2c+8, 2c+9 of column `col`) of one adapter straight from A [16, N] in global memory
+__device__ __forceinline__ void lora_bfrag_ldg(const unsigned short* __restrict__ A, int lda, int col, int c, uint32_t& b0, uint32_t& b1) {
+    const unsigned short* a = A + (size_t)(2 * c) * lda + col;
+    b0 = (uint32_t)__ldg(a) | ((uint32_t)__ldg(a + lda) << 16);
+    b1 = (uint32_t)__ldg(a + 8 * (size_t)lda) | ((uint32_t)__ldg(a + 9 * (size_t)lda) << 16);
+}
+
 template <bool B_MN, int SWIGLU = 0, bool LORA = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(g2_threads<SWIGLU, LORA>(), 1)
 gemm2_tcgen05_kernel(const GemmParams p,
@@ -199,15 +229,15 @@ gemm2_tcgen05_kernel(const GemmParams p,
             uint32_t xsel = 0;
             if constexpr (LORA) {
                 // every thread of the warpgroup is past the last bar.sync of its previous tile, so nobody still reads the old A.
-                // plain variant: ring stage 5 is free (5-deep ring); SwiGLU variant: stages 4 and 5 are free (4-deep ring), the A
-                // slots of those hold the second warpgroup's output staging buffers, the B slot of stage 4 the two A regions.
-                // Region of a warpgroup: [adapter][column of its 128][32 B record] then 4 x 1 KB hand-off buffers.
-                uint8_t* law = SWIGLU == 2 ? smem_b + (STAGES - 2) * G2_B_BYTES + wg * (G2_B_BYTES / 2)
-                                           : (wg == 0 ? smem_a : smem_b) + (STAGES - 1) * G2_A_BYTES;
+                // Both variants run a 5-deep ring and use ring stage 5. Plain: its A / B slot hold the two warpgroups' regions
+                // [adapter][column of its 128][32 B record] + 4 x 1 KB hand-off buffers. SwiGLU backward: the two slots are the
+                // second warpgroup's output staging buffers; its single adapter's B fragments come straight from global memory
+                // and the hand-off goes through the staging slots (lora_rank16_add8_slots), so nothing is staged here.
+                uint8_t* law = (wg == 0 ? smem_a : smem_b) + (STAGES - 1) * G2_A_BYTES;
                 la = smem_u32(law);
-                xb = la + (SWIGLU == 2 ? 1 : 3) * LA_AD_BYTES + q * LA_XBUF_BYTES;
+                xb = la + 3 * LA_AD_BYTES + q * LA_XBUF_BYTES;
                 const unsigned short* Ag = reinterpret_cast<const unsigned short*>(p.lr_A);
-                for (int idx = q * 32 + lane; idx < p.lr_na * LA_COLS; idx += 128) {      // one column of one adapter per thread
+                for (int idx = q * 32 + lane; SWIGLU != 2 && idx < p.lr_na * LA_COLS; idx += 128) {      // one column of one adapter per thread
                     const int a = idx / LA_COLS, tid = idx - a * LA_COLS;
                     const int ncol = n0 + wg * LA_COLS + tid;
                     uint32_t rec[8];
@@ -244,8 +274,11 @@ gemm2_tcgen05_kernel(const GemmParams p,
                 // with four warps (one per scheduler, latency-bound) the SwiGLU backward plus the adapter term made the epilogue
                 // longer than the K = 4096 main loop (ncu: tensor pipe 54 % active, against 86 % for the variant without adapters). Rolled over 8-column chunks: unrolled, this code overflowed the
                 // instruction cache and the warps stalled on instruction fetch.
-                uint8_t* cdg = wg == 0 ? smem_cd : smem_a + (STAGES - 2) * G2_A_BYTES;
-                uint8_t* cdu = cdg + CD_STAGE_BYTES;
+                uint8_t* cdg = wg == 0 ? smem_cd : smem_a + (STAGES - 1) * G2_A_BYTES;
+                uint8_t* cdu = wg == 0 ? smem_cd + CD_STAGE_BYTES : smem_b + (STAGES - 1) * G2_B_BYTES;
+                const unsigned short* Ag = reinterpret_cast<const unsigned short*>(p.lr_A);
+                uint32_t b0n, b1n;
+                lora_bfrag_ldg(Ag, p.lr_lda, n0 + wg * (G2_BN / 2) + (lane >> 2), lane & 3, b0n, b1n);
                 const int I = p.swiglu_I;
                 const bf16* gurow = p.sw_gu + (size_t)(m_ok ? m : 0) * p.sw_ld;
                 const int s_first = wg * (G2_BN / 128);
@@ -264,10 +297,12 @@ gemm2_tcgen05_kernel(const GemmParams p,
                     for (int ch = 0; ch < 8; ++ch) {
                         const int c0 = s * 64 + ch * 8;
                         const uint4 gv = gvn, uv = uvn;
-                        {   // gate / up of the NEXT chunk: the global round trip overlaps this chunk's math
+                        const uint32_t b0 = b0n, b1 = b1n;
+                        {   // gate / up and the adapter's B fragment of the NEXT chunk: the global round trip overlaps this chunk's math
                             const int cn = s_first * 64 + ((sl * 64 + ch * 8 + 8) & (G2_BN / 2 - 1));
                             gvn = __ldg(reinterpret_cast<const uint4*>(gurow + n0 + cn));
                             uvn = __ldg(reinterpret_cast<const uint4*>(gurow + I + n0 + cn));
+                            lora_bfrag_ldg(Ag, p.lr_lda, n0 + cn + (lane >> 2), lane & 3, b0n, b1n);
                         }
                         uint32_t r8[8];
                         tmem_ld8(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * G2_BN + c0), r8);
@@ -276,9 +311,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         unpack8(gv, g); unpack8(uv, u);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r8[j]) * p.alpha;
-                        lora_rank16_add8(dv, tf[0], la + (sl * 64 + ch * 8 + (lane >> 2)) * LA_REC_BYTES + (lane & 3) * 8, xb + xsel, lane,
-                                         (unsigned int)(kw >> (ch * 8)) & 0xFFu, p.lr_scale);
-                        xsel ^= 512u;
+                        lora_rank16_add8_slots(dv, tf[0], b0, b1, smem_u32(cdg), q, lane, ch, (unsigned int)(kw >> (ch * 8)) & 0xFFu, p.lr_scale);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const float d = bf2f(f2bf(dv[j]));

@@ -606,9 +606,8 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     p.lr_t = reinterpret_cast<const bf16*>(a.lr_t); p.lr_ldt = a.lr_ldt; p.lr_A = reinterpret_cast<const bf16*>(a.lr_A); p.lr_lda = a.lr_lda;
     for (int i = 0; i < 3; ++i) p.lr_bits[i] = reinterpret_cast<const unsigned long long*>(a.lr_bits[i]);
     p.lr_na = a.lr_na; p.lr_scale = a.lr_scale;
-    if (LORA && p.stages_used > G2_STAGES - 1) p.stages_used = G2_STAGES - 1;   // the last ring stage holds the staged adapter A columns
-    if (LORA && SWIGLU == 2) p.stages_used = G2_STAGES - 2;                     // ... and one more the second warpgroup's staging buffers
-    { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES - (LORA && SWIGLU == 2 ? 2 : (LORA || SWIGLU == 1) ? 1 : 0)) p.stages_used = atoi(g); }
+    if (LORA && p.stages_used > G2_STAGES - 1) p.stages_used = G2_STAGES - 1;   // the last ring stage holds the staged adapter columns / the second warpgroup's output staging
+    { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES - ((LORA || SWIGLU == 1) ? 1 : 0)) p.stages_used = atoi(g); }
     auto kern = gemm2_tcgen05_kernel<B_MN, SWIGLU, LORA>;
     static bool attr_set = false;
     if (!attr_set) {

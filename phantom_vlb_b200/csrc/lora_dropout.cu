@@ -77,8 +77,13 @@ constexpr int LM_BK = 64;
 constexpr int LM_BN = 64;             // B tile rows: 16 per adapter, <= 48 valid, the rest zero-filled by TMA
 constexpr int LM_A_BYTES = LM_BM * LM_BK * 2;     // 16 KB
 constexpr int LM_B_BYTES = LM_BN * LM_BK * 2;     // 8 KB
+constexpr int LM_W_BYTES = LM_BM * 8;             // 1 KB: one 64-bit keep word per tile row and adapter
 constexpr int LM_THREADS = 512;       // warp 0 TMA, 1 MMA, 2 TMEM, 3 idle, 4-7 epilogue, 8-15 transform
 constexpr int LM_XFORM_THREADS = 256;
+#ifndef LM_GROUPS_N
+#define LM_GROUPS_N 2
+#endif
+constexpr int LM_GROUPS = LM_GROUPS_N;  // transform warp groups taking k-blocks in turn (power of two)
 constexpr int LM_MAX_STAGES = 8;
 constexpr int LM_SMEM_BUDGET = 224 * 1024;
 
@@ -92,6 +97,7 @@ struct LoraMaskParams {
     int ld_out;
     int n_rows;                        // valid MMA-M rows: tokens (forward) / features (backward)
     int n_fb;                          // 64-feature blocks per token in the bit arrays
+    int bulk;                          // keep words travel in the TMA ring (full tiles only); 0: per-thread global loads
 };
 
 // keep-mask a 16-byte chunk (8 bf16) with 8 bits
@@ -109,7 +115,9 @@ __global__ void __launch_bounds__(LM_THREADS, 1)
 lora_masked_kernel(const LoraMaskParams p, const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int stage_bytes = p.n_ad * LM_A_BYTES + LM_B_BYTES;
+    // stage: n_ad masked copies of the x tile (the raw tile lands in copy 0) | B tile | (bulk) 1 KB of keep words per adapter
+    const int words_off = p.n_ad * LM_A_BYTES + LM_B_BYTES;
+    const int stage_bytes = words_off + (p.bulk ? p.n_ad * LM_W_BYTES : 0);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
     uint64_t* full_bar = bars;                              // [stages] TMA landed
     uint64_t* ready_bar = bars + LM_MAX_STAGES;             // [stages] masked copies written
@@ -123,7 +131,7 @@ lora_masked_kernel(const LoraMaskParams p, const __grid_constant__ CUtensorMap t
 
     if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
     if (warp == 1 && lane == 0) {
-        for (int i = 0; i < p.stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&ready_bar[i], LM_XFORM_THREADS / 32); mbar_init(&empty_bar[i], 1); }
+        for (int i = 0; i < p.stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&ready_bar[i], LM_XFORM_THREADS / 32 / LM_GROUPS); mbar_init(&empty_bar[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 128); }
         fence_barrier_init();
     }
@@ -148,10 +156,25 @@ lora_masked_kernel(const LoraMaskParams p, const __grid_constant__ CUtensorMap t
                 const int m0 = tile * LM_BM;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_expect_tx(&full_bar[stage], LM_A_BYTES + LM_B_BYTES);
+                    mbar_expect_tx(&full_bar[stage], LM_A_BYTES + LM_B_BYTES + (p.bulk ? p.n_ad * LM_W_BYTES : 0));
                     uint8_t* sa = smem + stage * stage_bytes;
                     uint8_t* sb = sa + p.n_ad * LM_A_BYTES;
                     const int k0 = kb * LM_BK;
+                    if (p.bulk) {
+                        // the keep words ride in the same ring as the tile they mask: requested by per-thread loads they queued
+                        // behind ~100 KB of in-flight tile traffic per SM and arrived several k-blocks late
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) {
+                            if (a >= p.n_ad) break;
+                            uint8_t* sw = sa + words_off + a * LM_W_BYTES;
+                            if constexpr (!A_MN) {          // 128 tokens of feature block kb
+                                bulk_load_1d(sw, p.bits[a] + (size_t)kb * p.n_tok + m0, LM_W_BYTES, &full_bar[stage]);
+                            } else {                        // 64 tokens of the tile's two feature blocks
+                                bulk_load_1d(sw, p.bits[a] + (size_t)(m0 >> 6) * p.n_tok + k0, LM_W_BYTES / 2, &full_bar[stage]);
+                                bulk_load_1d(sw + LM_W_BYTES / 2, p.bits[a] + (size_t)((m0 >> 6) + 1) * p.n_tok + k0, LM_W_BYTES / 2, &full_bar[stage]);
+                            }
+                        }
+                    }
                     if constexpr (!A_MN) {
                         tma_load_2d(&tmA, &full_bar[stage], sa, k0, m0);          // x [tokens, features]: rows = tokens
                         tma_load_2d(&tmB, &full_bar[stage], sb, k0, 0);           // A [16 n_ad, features]
@@ -201,52 +224,58 @@ lora_masked_kernel(const LoraMaskParams p, const __grid_constant__ CUtensorMap t
         }
     } else if (warp >= 8) {
         // ------------------------------------------------------------------ transform: masked copies of the x tile
+        // Two groups of four warps take alternate k-blocks: a stage's chain (wait for the tile -> LDS -> mask -> STS -> proxy fence
+        // -> arrive) is ~1000 cycles long while HBM delivers a tile every ~600, so with all eight warps on the same stage the
+        // chain, not the memory system, set the pace. A thread owns one 128-byte row (8 chunks) of its group's stage.
+        constexpr int GT = LM_XFORM_THREADS / LM_GROUPS;     // threads per group, each owning LM_BM / GT rows of its stage
         const int tt = threadIdx.x - 256;
-        const int row = tt >> 1, half = tt & 1;              // 128 rows of 128 B; a thread owns 4 of a row's 8 chunks
-        // the keep words of the NEXT k-block are requested before this one is waited for (a deeper, unrolled prefetch and an L2
-        // prefetcher warp were both tried and were slower: see DESIGN.md, LoRA dropout)
-        auto load_words = [&](int m0, int kb, unsigned int (&w)[3]) {
-            const int tok = A_MN ? kb * LM_BK + (row & 63) : m0 + row;
-            const int fb = A_MN ? (m0 >> 6) + (row >> 6) : kb;
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                w[a] = 0xFFFFFFFFu;
-                if (a < p.n_ad && tok < p.n_tok && fb < p.n_fb)
-                    w[a] = __ldg(reinterpret_cast<const unsigned int*>(p.bits[a] + (size_t)fb * p.n_tok + tok) + half);
-            }
-        };
-        unsigned int w[3], wn[3];
-        if (blockIdx.x < num_items) { int tile, kb0, kb1; item_range(blockIdx.x, tile, kb0, kb1); load_words(tile * LM_BM, kb0, wn); }
-        int stage = 0; uint32_t phase = 0;
+        const int grp = tt / GT, row0 = tt % GT;
         const uint32_t smem_base = smem_u32(smem);
+        int cyc = 0;                                         // k-blocks this CTA has been through (all groups count all of them)
         for (int t = blockIdx.x; t < num_items; t += gridDim.x) {
             int tile, kb0, kb1; item_range(t, tile, kb0, kb1);
             const int m0 = tile * LM_BM;
-            for (int kb = kb0; kb < kb1; ++kb) {
+            for (int kb = kb0; kb < kb1; ++kb, ++cyc) {
+                if ((cyc & (LM_GROUPS - 1)) != grp) continue;
+                const int stage = cyc % p.stages;
+                const uint32_t phase = (uint32_t)(cyc / p.stages) & 1u;
+                const uint32_t st = smem_base + stage * stage_bytes;
+                bool waited = false;
+#pragma unroll 1
+                for (int row = row0; row < LM_BM; row += GT) {
+                unsigned long long w[3] = {~0ull, ~0ull, ~0ull};
+                if (!p.bulk) {                            // ragged shapes: this row's keep words straight from global memory
+                    const int tok = A_MN ? kb * LM_BK + (row & 63) : m0 + row;
+                    const int fb = A_MN ? (m0 >> 6) + (row >> 6) : kb;
 #pragma unroll
-                for (int a = 0; a < 3; ++a) w[a] = wn[a];
-                if (kb + 1 < kb1) {
-                    load_words(m0, kb + 1, wn);
-                } else if (t + (int)gridDim.x < num_items) {
-                    int tile2, kb02, kb12; item_range(t + gridDim.x, tile2, kb02, kb12);
-                    load_words(tile2 * LM_BM, kb02, wn);
+                    for (int a = 0; a < 3; ++a)
+                        if (a < p.n_ad && tok < p.n_tok && fb < p.n_fb) w[a] = __ldg(p.bits[a] + (size_t)fb * p.n_tok + tok);
                 }
-                mbar_wait(&full_bar[stage], phase);
-                const uint32_t sa = smem_base + stage * stage_bytes + row * 128;
-                uint4 v[4];
+                if (!waited) { mbar_wait(&full_bar[stage], phase); waited = true; }
+                if (p.bulk) {                             // ... or landed with the tile
 #pragma unroll
-                for (int c = 0; c < 4; ++c) v[c] = lds128(sa + (((half * 4 + c) ^ (row & 7)) << 4));
+                    for (int a = 0; a < 3; ++a)
+                        if (a < p.n_ad) {
+                            uint32_t lo, hi;
+                            lds64(st + words_off + a * LM_W_BYTES + row * 8, lo, hi);
+                            w[a] = (unsigned long long)lo | ((unsigned long long)hi << 32);
+                        }
+                }
+                const uint32_t sa = st + row * 128;
+                uint4 v[8];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const int off = ((half * 4 + c) ^ (row & 7)) << 4;
+                for (int c = 0; c < 8; ++c) v[c] = lds128(sa + ((c ^ (row & 7)) << 4));
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int off = (c ^ (row & 7)) << 4;
 #pragma unroll
                     for (int a = 2; a >= 0; --a)          // adapter 0 is masked in place, so it goes last
-                        if (a < p.n_ad) sts128(sa + a * LM_A_BYTES + off, mask8(v[c], (w[a] >> (8 * c)) & 0xFFu));
+                        if (a < p.n_ad) sts128(sa + a * LM_A_BYTES + off, mask8(v[c], (unsigned int)(w[a] >> (8 * c)) & 0xFFu));
+                }
                 }
                 fence_proxy_async_smem();                 // generic-proxy writes -> visible to the tensor core's async proxy
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ready_bar[stage]);      // one arrival per warp
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp >= 4) {
@@ -303,7 +332,7 @@ lora_masked_kernel(const LoraMaskParams p, const __grid_constant__ CUtensorMap t
 template <bool A_MN>
 static int launch_lora_masked(const LoraMaskParams& p0, const CUtensorMap& tA, const CUtensorMap& tB, cudaStream_t stream) {
     LoraMaskParams p = p0;
-    const int stage_bytes = p.n_ad * LM_A_BYTES + LM_B_BYTES;
+    const int stage_bytes = p.n_ad * LM_A_BYTES + LM_B_BYTES + (p.bulk ? p.n_ad * LM_W_BYTES : 0);
     p.stages = LM_SMEM_BUDGET / stage_bytes;
     if (p.stages > LM_MAX_STAGES) p.stages = LM_MAX_STAGES;
     const int smem = p.stages * stage_bytes + 1024 + 512;
@@ -339,10 +368,17 @@ static int lm_common(LoraMaskParams& p, int n_tok, int n_feat, int n_ad, const v
     VLB_REQUIRE(n_ad >= 1 && n_ad <= 3 && n_feat % 64 == 0 && n_tok > 0, "lora_masked: adapters=%d features=%d tokens=%d", n_ad,
                 n_feat, n_tok);
     VLB_REQUIRE(b0 && (n_ad < 2 || b1) && (n_ad < 3 || b2), "lora_masked: missing mask bits for %d adapters", n_ad);
-    p.n_tok = n_tok; p.n_ad = n_ad; p.alpha = alpha; p.n_fb = n_feat / 64;
+    p.n_tok = n_tok; p.n_ad = n_ad; p.alpha = alpha; p.n_fb = n_feat / 64; p.bulk = 0;
     p.bits[0] = (const unsigned long long*)b0; p.bits[1] = (const unsigned long long*)b1; p.bits[2] = (const unsigned long long*)b2;
     p.out_bf16 = nullptr; p.out_f32 = nullptr;
     return 0;
+}
+
+static bool lm_words_aligned(const LoraMaskParams& p) {        // cp.async.bulk needs 16-byte aligned sources
+    if (getenv("VLB_LORA_WORDS_LDG")) return false;
+    for (int a = 0; a < p.n_ad; ++a)
+        if (reinterpret_cast<uintptr_t>(p.bits[a]) % 16 != 0) return false;
+    return p.n_tok % 2 == 0;
 }
 
 extern "C" int vlb_lora_down_masked(const void* x, int ldx, const void* A, int lda, void* xa, int ldxa, int n_tok, int n_feat,
@@ -357,6 +393,7 @@ extern "C" int vlb_lora_down_masked(const void* x, int ldx, const void* A, int l
     if ((rc = tmap2d_cached(&tB, A, n_feat, 16 * n_adapters, lda, LM_BK, LM_BN))) return rc;
     p.nk = n_feat / LM_BK; p.mt = ceil_div(n_tok, LM_BM); p.splits = 1;
     p.out_bf16 = (bf16*)xa; p.ld_out = ldxa; p.n_rows = n_tok;
+    p.bulk = n_tok % LM_BM == 0 && lm_words_aligned(p);          // full token tiles: 1 KB of words per (feature block, tile)
     return launch_lora_masked<false>(p, tA, tB, (cudaStream_t)stream);
 }
 
@@ -371,9 +408,18 @@ extern "C" int vlb_lora_grad_a_masked(const void* x, int ldx, const void* t, int
     if ((rc = tmap2d_cached(&tA, x, n_feat, n_tok, ldx, 64, LM_BK))) return rc;             // box: 64 features x 64 tokens
     if ((rc = tmap2d_cached(&tB, t, 16 * n_adapters, n_tok, ldt, 64, LM_BK))) return rc;     // box: 64 columns (zero-filled) x 64 tokens
     p.nk = ceil_div(n_tok, LM_BK); p.mt = ceil_div(n_feat, LM_BM);
-    int sp = num_sms() / p.mt;
-    if (sp > p.nk / 4) sp = p.nk / 4;
-    p.splits = sp > 1 ? sp : 1;
+    // split the token contraction so that the (feature tile, split) items fill whole waves of the persistent grid: 112 tiles
+    // on 148 SMs leave a quarter of the machine idle, 112 x 5 = 560 items are 3.8 waves (95 %); fewer splits = fewer atomics
+    const int sms = num_sms();
+    int best = 1; double best_eff = 0.0;
+    for (int sp = 1; sp <= 16 && sp <= (p.nk >= 4 ? p.nk / 4 : 1); ++sp) {
+        const int items = p.mt * sp;
+        const double eff = (double)items / ((double)ceil_div(items, sms) * sms);
+        if (eff > best_eff + 0.02) { best_eff = eff; best = sp; }
+    }
+    p.splits = best;
+    { const char* g = getenv("VLB_LORA_GRAD_SPLITS"); if (g && atoi(g) > 0) p.splits = atoi(g); }
     p.out_f32 = (float*)dA_f32; p.ld_out = ldda; p.n_rows = n_feat;
+    p.bulk = n_tok % LM_BK == 0 && n_feat % LM_BM == 0 && lm_words_aligned(p);   // full 64-token x 128-feature tiles
     return launch_lora_masked<true>(p, tA, tB, (cudaStream_t)stream);
 }

@@ -32,7 +32,7 @@ class Engine:
         # is ever written); other ranks fall back to materialised dropout(x) + a rank-r GEMM + masked add per projection input.
         self.lora_dropout = float(lora_dropout or 0.0)
         self.masked_lora = cfg.lora_r == 16 and os.environ.get("VLB_LORA_MASKED", "1") != "0"
-        self.pregen_masks = os.environ.get("VLB_PREGEN_MASKS", "1") != "0"
+        self.pregen_masks = os.environ.get("VLB_PREGEN_MASKS", "0") == "1"      # measured: no gain (tools/ab_dropout.py), off by default
         self.mask_stream, self.mask_events, self._pregen = None, None, None
         self.drop_bits = None       # test hook: dict filled with the packed keep masks keyed by (layer, site)
         self.drop_step = 0
