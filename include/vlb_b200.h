@@ -190,6 +190,16 @@ int vlb_ln1_affine_fwd(const void* u_f32, const void* sw_f32, const void* ln1_w,
 int vlb_ln1_affine_bwd(const void* dpooled_f32, const void* u_f32, const void* sw_f32, void* dg1_f32, void* db1_f32,
                        int B, int H, void* stream);
 
+/* q/k/v projection of a decoder layer with the rotary embedding fused into the GEMM epilogue (MistralAttention.forward:
+ * q_proj / k_proj / v_proj followed by apply_rotary_pos_emb, reached through videollama2_mistral.py:94-104; LoRA wrap
+ * src/litmodule/videollama2_vlb_litmodule.py:113-120): qkv[M, N] = x Wqkv^T (+ LoRA k-block A2/B2 as in vlb_gemm_bf16), then
+ * RoPE on the first n_rot_heads heads of D columns each (q and k; v passes through), position = row % S, cos/sin bf16 [S, D/2].
+ * Same rounding points as vlb_gemm_bf16 followed by vlb_rope (bit-identical). D == 128 with N % 256 == 0 runs fused on the
+ * CTA-pair kernel; any other shape runs the two kernels one after the other. */
+int vlb_gemm_qkv_rope(const void* x, int ldx, const void* wqkv, int ldw, void* qkv, int ldqkv, int M, int N, int K,
+                      const void* A2, int lda2, const void* B2, int ldb2, int K2, float alpha,
+                      const void* cos_tab, const void* sin_tab, int S, int n_rot_heads, int D, void* stream);
+
 /* Forward gate/up projection of the decoder MLP with SwiGLU fused into the GEMM epilogue (MistralMLP.forward:
  * act_fn(gate_proj(x)) * up_proj(x), reached through videollama2_mistral.py:94-104): gu[M, 2I] (kept for the backward) and
  * act[M, I] leave the kernel together; wgu is [2I, K] gate rows then up rows; A2/B2 = the fused LoRA k-block as in

@@ -33,7 +33,7 @@ constexpr int G2_TMEM_COLS = 512;
 // The plain variant (SWIGLU == 0) runs EIGHT epilogue warps (384 threads): two warpgroups, each owning 128 of the tile's 256
 // columns with its own staging buffer, named barrier and TMA-store issuer. With four warps the K = 1024 ViT GEMMs whose
 // epilogue carries an activation or a residual were epilogue-bound (fc1 650, o-proj 500 TF/s against 1350 plain).
-template <int SWIGLU, bool LORA = false> __host__ __device__ constexpr int g2_threads() { return (SWIGLU == 0 || (SWIGLU == 2 && LORA)) ? 384 : 256; }
+template <int SWIGLU, bool LORA = false> __host__ __device__ constexpr int g2_threads() { return (SWIGLU == 0 || SWIGLU == 3 || (SWIGLU == 2 && LORA)) ? 384 : 256; }
 
 // LORA_EPI (dX GEMMs under LoRA dropout): the adapter branch of the input gradient, 1/(1-p) * keep_a . (t_a A_a), cannot ride in
 // the accumulator as a k-block (the keep mask sits between the rank-16 product and the sum), so the epilogue forms it beside the
@@ -450,6 +450,62 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         tma_store_2d(&tmAct, cda, f0 + s * 64, m0);
                         tma_store_commit();
                     }
+                }
+                continue;
+            }
+            if constexpr (SWIGLU == 3) {
+                // RoPE (q/k/v projection, head_dim 128): this warpgroup owns one head = two 64-column chunks, x1 = columns [0, 64) and
+                // x2 = [64, 128) of the head; out1 = x1 cos - x2 sin, out2 = x2 cos + x1 sin with the stand-alone kernel's rounding
+                // (projection -> bf16, products -> bf16, sum -> bf16). Heads at or beyond rope_ncols (v) pass through.
+                uint8_t* cd0 = wg == 0 ? smem_cd : smem_a + (STAGES - 1) * G2_A_BYTES;
+                uint8_t* cd1 = wg == 0 ? smem_cd + CD_STAGE_BYTES : smem_b + (STAGES - 1) * G2_B_BYTES;
+                const int nh0 = n0 + wg * (G2_BN / 2);
+                const bool rot = nh0 < p.rope_ncols;
+                const size_t pos = m_ok ? (size_t)(m % p.rope_S) : 0;
+                const bf16* cr = p.rope_cos + pos * 64;
+                const bf16* sr = p.rope_sin + pos * 64;
+                if (issuer) tma_store_wait_read<0>();
+                asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint4 cv[4], sv[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {               // requested before the TMEM wait
+                        cv[c] = __ldg(reinterpret_cast<const uint4*>(cr + h * 32 + c * 8));
+                        sv[c] = __ldg(reinterpret_cast<const uint4*>(sr + h * 32 + c * 8));
+                    }
+                    uint32_t ra[32], rb[32];
+                    const uint32_t tcol = (uint32_t)(as * G2_BN + wg * (G2_BN / 2) + h * 32);
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tcol, ra);
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tcol + 64, rb);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        float cs[8], sn[8], oa[8], ob[8];
+                        unpack8(cv[c], cs); unpack8(sv[c], sn);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float a = bf2f(f2bf(__uint_as_float(ra[c * 8 + j]) * p.alpha));
+                            const float b = bf2f(f2bf(__uint_as_float(rb[c * 8 + j]) * p.alpha));
+                            oa[j] = rot ? bf2f(f2bf(a * cs[j])) + bf2f(f2bf(-b * sn[j])) : a;
+                            ob[j] = rot ? bf2f(f2bf(b * cs[j])) + bf2f(f2bf(a * sn[j])) : b;
+                        }
+                        uint4 ua, ub;
+                        ua.x = pack_bf16(oa[0], oa[1]); ua.y = pack_bf16(oa[2], oa[3]); ua.z = pack_bf16(oa[4], oa[5]); ua.w = pack_bf16(oa[6], oa[7]);
+                        ub.x = pack_bf16(ob[0], ob[1]); ub.y = pack_bf16(ob[2], ob[3]); ub.z = pack_bf16(ob[4], ob[5]); ub.w = pack_bf16(ob[6], ob[7]);
+                        const int off = row * 128 + (((h * 4 + c) ^ (row & 7)) << 4);
+                        sts128(smem_u32(cd0) + off, ua);
+                        sts128(smem_u32(cd1) + off, ub);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive_cluster(&tempty_bar[as], 0);
+                fence_proxy_async_smem();
+                asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
+                if (issuer) {
+                    tma_store_2d(&tmC, cd0, nh0, m0);
+                    tma_store_2d(&tmC, cd1, nh0 + 64, m0);
+                    tma_store_commit();
                 }
                 continue;
             }

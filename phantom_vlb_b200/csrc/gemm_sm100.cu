@@ -65,6 +65,8 @@ struct GemmParams {
     // t [M, 16 lr_na] bf16, A [16 lr_na, N] bf16, keep bits as 64-bit words [N / 64][M] per adapter (lora_dropout.cu)
     const bf16* lr_t; int lr_ldt; const bf16* lr_A; int lr_lda;
     const unsigned long long* lr_bits[3]; int lr_na; float lr_scale;
+    // pair kernel, epilogue mode 3 (qkv projection): RoPE on the heads whose columns lie below rope_ncols, position = row % rope_S
+    const bf16* rope_cos; const bf16* rope_sin; int rope_S; int rope_ncols;
 };
 
 __device__ __forceinline__ void tile_coords(int t, int mt, int nt, int GROUP_M, int& mb, int& nb) {
@@ -492,6 +494,8 @@ struct GemmArgs {
     // optional masked adapter term in the pair kernel's epilogue (LORA_EPI, see GemmParams)
     const void* lr_t = nullptr; int lr_ldt = 0; const void* lr_A = nullptr; int lr_lda = 0;
     const void* lr_bits[3] = {nullptr, nullptr, nullptr}; int lr_na = 0; float lr_scale = 1.f;
+    // optional RoPE epilogue (pair kernel, mode 3)
+    const void* rope_cos = nullptr; const void* rope_sin = nullptr; int rope_S = 1; int rope_ncols = 0;
 };
 
 template <int BN, bool A_MN, bool B_MN, bool ADAM = false>
@@ -602,12 +606,13 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     // algorithmic bytes: a wave of 74 256x256 tiles touches ~17 distinct 256-row panels of K columns each, and the panels of
     // consecutive waves (8 x 7-15 MB of A, all of B) no longer fit the 126 MB L2 at these K.
     p.stages_used = a.K1 >= 8192 ? 4 : G2_STAGES;
-    if (SWIGLU == 1) p.stages_used = G2_STAGES - 1;      // the last ring stage is the third epilogue staging buffer
+    if (SWIGLU == 1 || SWIGLU == 3) p.stages_used = G2_STAGES - 1;      // the last ring stage is epilogue staging (third buffer / second warpgroup's pair)
+    p.rope_cos = reinterpret_cast<const bf16*>(a.rope_cos); p.rope_sin = reinterpret_cast<const bf16*>(a.rope_sin); p.rope_S = a.rope_S; p.rope_ncols = a.rope_ncols;
     p.lr_t = reinterpret_cast<const bf16*>(a.lr_t); p.lr_ldt = a.lr_ldt; p.lr_A = reinterpret_cast<const bf16*>(a.lr_A); p.lr_lda = a.lr_lda;
     for (int i = 0; i < 3; ++i) p.lr_bits[i] = reinterpret_cast<const unsigned long long*>(a.lr_bits[i]);
     p.lr_na = a.lr_na; p.lr_scale = a.lr_scale;
     if (LORA && p.stages_used > G2_STAGES - 1) p.stages_used = G2_STAGES - 1;   // the last ring stage holds the staged adapter columns / the second warpgroup's output staging
-    { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES - ((LORA || SWIGLU == 1) ? 1 : 0)) p.stages_used = atoi(g); }
+    { const char* g = getenv("VLB_GEMM_STAGES"); if (g && atoi(g) > 0 && atoi(g) <= G2_STAGES - ((LORA || SWIGLU == 1 || SWIGLU == 3) ? 1 : 0)) p.stages_used = atoi(g); }
     auto kern = gemm2_tcgen05_kernel<B_MN, SWIGLU, LORA>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -702,6 +707,32 @@ extern "C" int vlb_head_adamw_fused(const void* dpred, int ld_dpred, const void*
     a.ad_bc1 = 1.f - powf(beta1, (float)step); a.ad_bc2 = 1.f - powf(beta2, (float)step);
     a.ad_max_norm = max_norm; a.ad_gscale = grad_scale; a.ad_two_lambda = 2.f * l2_lambda;
     return vlb::gemm_dispatch(a, 256, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// q/k/v projection of a decoder layer with RoPE fused into the epilogue (pair kernel, head_dim 128): the two warpgroups of a CTA
+// own one head each (128 of the tile's 256 columns), read both halves of the head from TMEM and write the rotated pair, with the
+// rounding points of the stand-alone kernel (bf16 projection, bf16 products, bf16 sum). Shapes the pair kernel does not take
+// (narrow test models) run the plain GEMM followed by vlb_rope.
+extern "C" int vlb_rope(void* qkv, int ld, const void* cos_tab, const void* sin_tab, long long M, int S, int nheads, int D,
+                        int inverse, void* stream);
+extern "C" int vlb_gemm_qkv_rope(const void* x, int ldx, const void* wqkv, int ldw, void* qkv, int ldqkv, int M, int N, int K,
+                                 const void* A2, int lda2, const void* B2, int ldb2, int K2, float alpha,
+                                 const void* cos_tab, const void* sin_tab, int S, int n_rot_heads, int D, void* stream) {
+    VLB_REQUIRE(M > 0 && N > 0 && K > 0 && S > 0 && D > 0 && n_rot_heads * D <= N, "gemm_qkv_rope: M=%d N=%d K=%d S=%d heads=%d D=%d",
+                M, N, K, S, n_rot_heads, D);
+    vlb::GemmArgs a;
+    a.A1 = x; a.lda1 = ldx; a.K1 = K; a.B1 = wqkv; a.ldb1 = ldw;
+    a.A2 = A2; a.lda2 = lda2; a.K2 = (A2 && B2) ? K2 : 0; a.B2 = B2; a.ldb2 = ldb2;
+    a.C = qkv; a.ldc = ldqkv; a.c_is_f32 = 0; a.accum = 0; a.M = M; a.N = N; a.alpha = alpha;
+    a.bias = nullptr; a.residual = nullptr; a.ldr = 0; a.act = 0;
+    a.a_mn = 0; a.b_mn = 0; a.max_ctas = 0; a.split_k = 1;
+    const bool fuse = D == 128 && N % vlb::G2_BN == 0 && vlb::use_pair_kernel(a) && !getenv("VLB_ROPE_UNFUSED");
+    if (!fuse) {
+        if (int rc = vlb::gemm_dispatch(a, 0, reinterpret_cast<cudaStream_t>(stream))) return rc;
+        return vlb_rope(qkv, ldqkv, cos_tab, sin_tab, M, S, n_rot_heads, D, 0, stream);
+    }
+    a.rope_cos = cos_tab; a.rope_sin = sin_tab; a.rope_S = S; a.rope_ncols = n_rot_heads * D;
+    return vlb::launch_gemm2<false, 3>(a, reinterpret_cast<cudaStream_t>(stream));
 }
 
 // Forward gate/up projection with SwiGLU fused into the epilogue (pair kernel): gu[M, 2I] = x Wgu^T (+ LoRA k-block) and

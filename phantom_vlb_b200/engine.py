@@ -324,10 +324,12 @@ class Engine:
             ops.rmsnorm_fwd(x, L["ln1_w"], cfg.rms_eps, out=b["xn1"], rstd=b["rstd1"])
             if lora:
                 self._lora_down(b["xn1"], T.w(p + "Acat_qkv"), b["xa1"], l, 0, save)
-                self.gemm(b["xn1"], L["wqkv"], b["qkv"], a2=b["xa1"], b2=bc["qkv"])
-            else:
-                self.gemm(b["xn1"], L["wqkv"], b["qkv"])
-            ops.rope_(b["qkv"], W.llm["cos"], W.llm["sin"], S, cfg.heads + cfg.kv_heads, D)
+            # q/k/v projection (+ fused LoRA k-block) with RoPE in the GEMM epilogue (head_dim 128; other widths: GEMM, then rope)
+            xa1, bq = (b["xa1"], bc["qkv"]) if lora else (None, None)
+            Nq = L["wqkv"].shape[0]
+            self._timed(2.0 * M * Nq * (cfg.hidden + (xa1.shape[1] if lora else 0)), (M, Nq, cfg.hidden, xa1.shape[1] if lora else 0),
+                        lambda: ops.gemm_qkv_rope(b["xn1"], L["wqkv"], b["qkv"], W.llm["cos"], W.llm["sin"], S,
+                                                  cfg.heads + cfg.kv_heads, D, a2=xa1, b2=bq))
             ops.attn_fwd_into(b["qkv"], b["o"], b["lse"], B, S, cfg.heads, cfg.kv_heads, D, True)
             if lora:
                 self._lora_down(b["o"], T.w(p + "A_o"), b["xa2"], l, 1, save)
@@ -343,7 +345,7 @@ class Engine:
                 self.gemm(b["act"], L["wd"], nxt, a2=b["xa4"], b2=bc["d"], residual=b["h1"])
             else:
                 self.gemm(b["act"], L["wd"], nxt, residual=b["h1"])
-            self.launches += 4                          # rmsnorm x2, rope, attention (gateup counts its own)
+            self.launches += 3 + (0 if D == 128 else 1)  # rmsnorm x2, attention (+ the stand-alone rope when it is not fused)
             x = nxt
         return x
 

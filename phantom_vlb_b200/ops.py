@@ -47,6 +47,24 @@ def gemm(a, b, out=None, *, a2=None, b2=None, alpha=1.0, bias=None, residual=Non
     return out
 
 
+def gemm_qkv_rope(x, wqkv, qkv, cos, sin, S, n_rot_heads, D, *, a2=None, b2=None, alpha=1.0):
+    """qkv[M, N] = x @ wqkv.T (+ a2 @ b2.T), then RoPE on the first n_rot_heads heads (position = row % S), in one launch when
+    D == 128 (CTA-pair GEMM with the rotation in its epilogue); bit-identical to gemm() followed by rope_()."""
+    _chk(x, torch.bfloat16), _chk(wqkv, torch.bfloat16), _chk(qkv, torch.bfloat16)
+    M, K = x.shape
+    N = wqkv.shape[0]
+    assert wqkv.shape == (N, K) and qkv.shape == (M, N) and cos.dtype == torch.bfloat16 and cos.shape[1] == D // 2
+    K2 = 0
+    if a2 is not None:
+        _chk(a2, torch.bfloat16), _chk(b2, torch.bfloat16)
+        K2 = a2.shape[1]
+        assert b2.shape == (N, K2) and a2.shape[0] == M
+    _l.call("vlb_gemm_qkv_rope", _l.ptr(x), x.stride(0), _l.ptr(wqkv), wqkv.stride(0), _l.ptr(qkv), qkv.stride(0), M, N, K,
+            _l.ptr(a2), a2.stride(0) if a2 is not None else 0, _l.ptr(b2), b2.stride(0) if b2 is not None else 0, K2,
+            float(alpha), _l.ptr(cos), _l.ptr(sin), int(S), int(n_rot_heads), int(D), _l.cur_stream())
+    return qkv
+
+
 def gemm_gateup_swiglu(x, wgu, gu, act, *, a2=None, b2=None, alpha=1.0):
     """gu[M, 2I] = x @ wgu.T (+ a2 @ b2.T) and act[M, I] = silu(gu[:, :I]) * gu[:, I:] from one CTA-pair GEMM launch."""
     _chk(x, torch.bfloat16), _chk(wgu, torch.bfloat16), _chk(gu, torch.bfloat16), _chk(act, torch.bfloat16)

@@ -183,3 +183,37 @@ def test_gemm_down_dx_swiglu_bwd_fused(M, I, H, R):
     sg = torch.sigmoid(gf)
     ref32 = torch.cat([d32 * uf * sg * (1 + gf * (1 - sg)), d32 * gf * sg], dim=1)
     _close(dgu, ref32, tol=2e-2)
+
+
+@pytest.mark.parametrize("M,Hq,Hkv,D,K,R,S", [(16384, 32, 8, 128, 4096, 48, 2048), (4096 + 72, 8, 2, 128, 512, 0, 521),
+                                              (256, 4, 2, 32, 128, 48, 64), (300, 2, 2, 128, 256, 16, 100)])
+def test_gemm_qkv_rope_fused(M, Hq, Hkv, D, K, R, S):
+    """q/k/v projection (+ LoRA k-block) with RoPE in the pair kernel's epilogue == GEMM then the rope kernel, bit for bit (the 7B
+    shape and a ragged one run fused; head_dim 32 and a grid too small for the pair kernel take the two-kernel route inside the
+    entry point), and against fp32 torch with HF's rotate_half formula."""
+    from phantom_vlb_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(M + K + D)
+    N = (Hq + 2 * Hkv) * D
+    x = torch.randn((M, K), device="cuda", generator=g).bfloat16()
+    w = (torch.randn((N, K), device="cuda", generator=g) * K ** -0.5).bfloat16()
+    a2 = torch.randn((M, R), device="cuda", generator=g).bfloat16() if R else None
+    b2 = (torch.randn((N, R), device="cuda", generator=g) * 0.1).bfloat16() if R else None
+    inv = 1.0 / (10000.0 ** (torch.arange(0, D, 2, device="cuda").float() / D))
+    ang = torch.arange(S, device="cuda").float()[:, None] * inv[None, :]
+    cos, sin = ang.cos().bfloat16(), ang.sin().bfloat16()
+    ref = ops.gemm(x, w, a2=a2, b2=b2)
+    plain = ref.clone()
+    ops.rope_(ref, cos, sin, S, Hq + Hkv, D)
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.gemm_qkv_rope(x, w, out, cos, sin, S, Hq + Hkv, D, a2=a2, b2=b2)
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref), "fused qkv+rope differs from gemm -> rope: max %g" % float((out.float() - ref.float()).abs().max())
+    assert torch.equal(out[:, (Hq + Hkv) * D:], plain[:, (Hq + Hkv) * D:])          # v passes through
+    p32 = (x.float() @ w.float().t() + (a2.float() @ b2.float().t() if R else 0)).view(M, Hq + 2 * Hkv, D)
+    pos = torch.arange(M, device="cuda") % S
+    c = torch.cat([cos, cos], 1).float()[pos][:, None, :]
+    s = torch.cat([sin, sin], 1).float()[pos][:, None, :]
+    rh = torch.cat([-p32[..., D // 2:], p32[..., :D // 2]], -1)
+    r32 = p32.clone()
+    r32[:, :Hq + Hkv] = (p32 * c + rh * s)[:, :Hq + Hkv]
+    _close(out, r32.view(M, N), tol=2e-2)
