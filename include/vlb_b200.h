@@ -239,6 +239,10 @@ int vlb_adamw_step(void* param_f32, const void* grad_f32, void* m_f32, void* v_f
                    float weight_decay, int step, float max_norm, float grad_scale, void* stream);
 int vlb_f32_to_bf16(const void* src, void* dst, long long n, void* stream);
 int vlb_copy2d(const void* src, int lds, void* dst, int ldd, int rows, int cols, int transpose, void* stream);
+/* n bf16 transposes dst_i[c, r] = src_i[r, c] in one launch; desc = device int64 [n, 6] rows of (src pointer, dst pointer,
+ * lds, ldd, rows, cols). Used once per optimiser step to restage every layer's LoRA B^T [r, N] as the [N, r] column blocks the
+ * fused k-block of vlb_gemm_bf16 reads (peft keeps lora_B as nn.Linear weights [N, r]: litmodule.py:113-120). */
+int vlb_transpose2d_batch(const void* desc_i64, int n, int blocks_per_item, void* stream);
 
 /* ------------------------------------------------------------------ per-parcel Pearson r (single pass, fp64 moments)
  * stats_f64 [5, P] accumulates (sum x, sum y, sum x^2, sum y^2, sum xy) of nan_to_num'd inputs; the raw sums are

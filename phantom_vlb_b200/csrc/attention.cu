@@ -265,7 +265,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 u.z = pack_bf16(__uint_as_float(o[c8 * 8 + 4]) * inv_l, __uint_as_float(o[c8 * 8 + 5]) * inv_l);
                 u.w = pack_bf16(__uint_as_float(o[c8 * 8 + 6]) * inv_l, __uint_as_float(o[c8 * 8 + 7]) * inv_l);
                 const int chunk = ((c0 & 63) >> 3) + c8;
-                *reinterpret_cast<uint4*>(dst + ((chunk ^ (row & 7)) << 4)) = u;
+                sts128(smem_u32(dst) + ((chunk ^ (row & 7)) << 4), u);
             }
         }
         if (p.lse != nullptr && qrow < p.S)

@@ -384,8 +384,8 @@ gemm2_tcgen05_kernel(const GemmParams p,
                             vg.x = pack_bf16(dg[0], dg[1]); vg.y = pack_bf16(dg[2], dg[3]); vg.z = pack_bf16(dg[4], dg[5]); vg.w = pack_bf16(dg[6], dg[7]);
                             vu.x = pack_bf16(du[0], du[1]); vu.y = pack_bf16(du[2], du[3]); vu.z = pack_bf16(du[4], du[5]); vu.w = pack_bf16(du[6], du[7]);
                             const int off = row * 128 + (((h * 4 + c) ^ (row & 7)) << 4);
-                            *reinterpret_cast<uint4*>(cdg + off) = vg;
-                            *reinterpret_cast<uint4*>(cdu + off) = vu;
+                            sts128(smem_u32(cdg) + off, vg);
+                            sts128(smem_u32(cdu) + off, vu);
                         }
                     }
                     if (s == G2_BN / 64 - 1) {
@@ -433,9 +433,9 @@ gemm2_tcgen05_kernel(const GemmParams p,
                             vu.x = pack_bf16(u[0], u[1]); vu.y = pack_bf16(u[2], u[3]); vu.z = pack_bf16(u[4], u[5]); vu.w = pack_bf16(u[6], u[7]);
                             va.x = pack_bf16(a[0], a[1]); va.y = pack_bf16(a[2], a[3]); va.z = pack_bf16(a[4], a[5]); va.w = pack_bf16(a[6], a[7]);
                             const int off = row * 128 + (((h * 4 + c) ^ (row & 7)) << 4);
-                            *reinterpret_cast<uint4*>(cdg + off) = vg;
-                            *reinterpret_cast<uint4*>(cdu + off) = vu;
-                            *reinterpret_cast<uint4*>(cda + off) = va;
+                            sts128(smem_u32(cdg) + off, vg);
+                            sts128(smem_u32(cdu) + off, vu);
+                            sts128(smem_u32(cda) + off, va);
                         }
                     }
                     if (s == G2_HALF_N / 64 - 1) {
@@ -617,7 +617,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);
                         u.z = pack_bf16(v[4], v[5]); u.w = pack_bf16(v[6], v[7]);
                         const int chunk = h * 4 + c;
-                        *reinterpret_cast<uint4*>(cd + row * 128 + ((chunk ^ (row & 7)) << 4)) = u;
+                        sts128(smem_u32(cd) + row * 128 + ((chunk ^ (row & 7)) << 4), u);
                     }
                 }
                 if (sl == G2_BN / 128 - 1) {                // this thread's TMEM reads of the accumulator stage are done

@@ -335,7 +335,7 @@ gemm_tcgen05_kernel(const GemmParams p,
                         u.x = pack_bf16(v[0], v[1]); u.y = pack_bf16(v[2], v[3]);
                         u.z = pack_bf16(v[4], v[5]); u.w = pack_bf16(v[6], v[7]);
                         const int chunk = h * 4 + c;        // 16-byte chunk index inside the 128-byte row
-                        *reinterpret_cast<uint4*>(cd + row * 128 + ((chunk ^ (row & 7)) << 4)) = u;
+                        sts128(smem_u32(cd) + row * 128 + ((chunk ^ (row & 7)) << 4), u);
                     }
                 }
                 if (s == BN / 64 - 1) {                     // all TMEM reads of this accumulator stage are done

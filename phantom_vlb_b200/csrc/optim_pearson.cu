@@ -77,6 +77,20 @@ __global__ void transpose2d_kernel(const bf16* __restrict__ src, int lds, bf16* 
     }
 }
 
+// The same transpose for a whole table of (src, dst) pairs in ONE launch: blockIdx.y picks the row of desc = int64 [n, 6] =
+// (src, dst, lds, ldd, rows, cols). The per-step refresh of the staged LoRA B matrices was 7 x 32 launches of ~8 us each.
+__global__ void transpose2d_batch_kernel(const long long* __restrict__ desc) {
+    const long long* d = desc + (size_t)blockIdx.y * 6;
+    const bf16* src = reinterpret_cast<const bf16*>(d[0]);
+    bf16* dst = reinterpret_cast<bf16*>(d[1]);
+    const int lds = (int)d[2], ldd = (int)d[3], rows = (int)d[4], cols = (int)d[5];
+    const long long total = (long long)rows * cols;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i / rows), r = (int)(i % rows);
+        dst[(size_t)c * ldd + r] = src[(size_t)r * lds + c];
+    }
+}
+
 // --------------------------------------------------------------------------------------------- Pearson
 template <typename T> __device__ __forceinline__ float ld_clean(const T* p);
 template <> __device__ __forceinline__ float ld_clean<float>(const float* p) {
@@ -243,6 +257,12 @@ extern "C" int vlb_copy2d(const void* src, int lds, void* dst, int ldd, int rows
     else
         copy2d_kernel<<<grid1d(total, 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)src, lds, (bf16*)dst, ldd, rows, cols);
     return check_launch("copy2d");
+}
+
+extern "C" int vlb_transpose2d_batch(const void* desc_i64, int n, int blocks_per_item, void* stream) {
+    VLB_REQUIRE(n > 0 && n <= 65535 && blocks_per_item > 0, "transpose2d_batch: n=%d blocks=%d", n, blocks_per_item);
+    transpose2d_batch_kernel<<<dim3(blocks_per_item, n), 256, 0, (cudaStream_t)stream>>>((const long long*)desc_i64);
+    return check_launch("transpose2d_batch");
 }
 
 extern "C" int vlb_pearson_update(const void* preds, const void* targets, void* stats_f64, long long N, long long P,

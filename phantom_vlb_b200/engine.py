@@ -703,7 +703,7 @@ class Engine:
         else:
             adamw(0, T.numel)
         T.stage_b()
-        self.launches += 7 * T.lora_layers
+        self.launches += 1 if T.lora_layers else 0
 
     def train_step(self, batch, lr, **opt):
         out, _ = self.loss_and_grads(batch)

@@ -304,16 +304,25 @@ class Trainables:
         self.stage_b()
 
     def stage_b(self):
-        cfg = self.cfg
-        r, D = cfg.lora_r, cfg.head_dim
-        nq, nkv, I = cfg.heads * D, cfg.kv_heads * D, cfg.mlp
-        for l in range(self.lora_layers):
-            p = "layers.%d." % l
-            bc = self.bcat[l]
-            ops.copy2d(self.w(p + "Bt_q"), bc["qkv"][0:nq, 0:r], r, nq, transpose=True)
-            ops.copy2d(self.w(p + "Bt_k"), bc["qkv"][nq:nq + nkv, r:2 * r], r, nkv, transpose=True)
-            ops.copy2d(self.w(p + "Bt_v"), bc["qkv"][nq + nkv:, 2 * r:3 * r], r, nkv, transpose=True)
-            ops.copy2d(self.w(p + "Bt_o"), bc["o"], r, cfg.hidden, transpose=True)
-            ops.copy2d(self.w(p + "Bt_g"), bc["gu"][0:I, 0:r], r, I, transpose=True)
-            ops.copy2d(self.w(p + "Bt_u"), bc["gu"][I:, r:2 * r], r, I, transpose=True)
-            ops.copy2d(self.w(p + "Bt_d"), bc["d"], r, cfg.hidden, transpose=True)
+        """LoRA B^T [r, N] (bf16 working copy) -> the [N, r] column blocks of the staged Bcat matrices: one batched launch over
+        a descriptor table built once (source and destination buffers never move)."""
+        from . import lib as _l
+        if not self.lora_layers:
+            return
+        if getattr(self, "_stage_desc", None) is None:
+            cfg = self.cfg
+            r, D = cfg.lora_r, cfg.head_dim
+            nq, nkv, I = cfg.heads * D, cfg.kv_heads * D, cfg.mlp
+            rows = []
+            for l in range(self.lora_layers):
+                p = "layers.%d." % l
+                bc = self.bcat[l]
+                for src, dst, n in ((self.w(p + "Bt_q"), bc["qkv"][0:nq, 0:r], nq), (self.w(p + "Bt_k"), bc["qkv"][nq:nq + nkv, r:2 * r], nkv),
+                                    (self.w(p + "Bt_v"), bc["qkv"][nq + nkv:, 2 * r:3 * r], nkv), (self.w(p + "Bt_o"), bc["o"], cfg.hidden),
+                                    (self.w(p + "Bt_g"), bc["gu"][0:I, 0:r], I), (self.w(p + "Bt_u"), bc["gu"][I:, r:2 * r], I),
+                                    (self.w(p + "Bt_d"), bc["d"], cfg.hidden)):
+                    assert src.shape == (r, n) and dst.shape == (n, r)
+                    rows.append([src.data_ptr(), dst.data_ptr(), src.stride(0), dst.stride(0), r, n])
+            self._stage_desc = torch.tensor(rows, dtype=torch.int64, device=self.param_bf16.device)
+            self._stage_blocks = max(1, min(64, (r * max(I, nq) + 2047) // 2048))
+        _l.call("vlb_transpose2d_batch", _l.ptr(self._stage_desc), self._stage_desc.shape[0], self._stage_blocks, _l.cur_stream())
