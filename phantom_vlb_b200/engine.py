@@ -369,6 +369,7 @@ class Engine:
         t16 = self.buf("bw_t16", (M, r))
         dxa = self.buf("bw_dx_a", (M, H))
         dxb = self.buf("bw_dx_b", (M, H))
+        pending_hi = cfg.layers                             # layers [l, pending_hi) have final gradients not yet handed to grad_ready
         for l in range(cfg.layers - 1, -1, -1):
             L, b, bc = W.llm_layers[l], self._layer_bufs(l, M), T.bcat[l]
             p = "layers.%d." % l
@@ -414,8 +415,11 @@ class Engine:
             self.gemm(b["xa1"][:, r:2 * r], dqkv[:, nq:nq + nkv], T.g(p + "Bt_k"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.gemm(b["xa1"][:, 2 * r:3 * r], dqkv[:, nq + nkv:], T.g(p + "Bt_v"), a_mn=True, b_mn=True, out_f32=True, accumulate=True)
             self.launches += 6 if fused_bwd else 7
-            if self.grad_ready is not None and l % self.grad_chunk_layers == 0:
-                hi_l = min(cfg.layers, l + self.grad_chunk_layers)
+            # chunks of grad_chunk_layers layers, except that the last chunk is split into layers [1, chunk) and layer 0 alone: the
+            # reduce launched after layer 0 is the one nothing overlaps, so it should be as small as possible
+            if self.grad_ready is not None and (l % self.grad_chunk_layers == 0 or l == 1):
+                hi_l = pending_hi
+                pending_hi = l
                 lo = T.offsets["layers.%d.Acat_qkv" % l][0]
                 hi = T.offsets["layers.%d.Acat_qkv" % hi_l][0] if hi_l < cfg.layers else T.offsets["ridge_w"][0]
                 # every kernel that writes these layers' slice of T.grad has been enqueued above (the q/k/v input-gradient GEMM
