@@ -33,7 +33,10 @@ typedef __nv_bfloat16 bf16;
 typedef __nv_bfloat162 bf162;
 
 __device__ __forceinline__ float bf2f(bf16 v) { return __bfloat162float(v); }
-__device__ __forceinline__ bf16 f2bf(float v) { return __float2bfloat16_rn(v); }
+// through the packed convert (cvt.rn.bf16x2.f32 -> F2FP on the ALU pipe): the scalar cvt.rn.bf16.f32 compiles to F2F, which shares
+// the quarter-rate conversion/XU pipe -- the row kernels that emulate the reference's bf16 rounding points (3 roundings per element
+// in hrf_pool) were bound by it. Same round-to-nearest-even result.
+__device__ __forceinline__ bf16 f2bf(float v) { return __floats2bfloat162_rn(v, 0.f).x; }
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     bf162 v = __floats2bfloat162_rn(lo, hi);
