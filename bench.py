@@ -169,8 +169,8 @@ def run_ours(args):
     hosts = host_batches(mc, B, 2, seed=1234 + rank)         # rank-private clips
     devs = [{k: v.to(dev) for k, v in h.items()} for h in hosts]
     h2d = sum(v.numel() * v.element_size() for v in hosts[0].values())
-    # data parallel: every finished slice of the flat gradient (head, then groups of 4 decoder layers) is all-reduced on a side
-    # stream while the backward of the earlier layers runs; only the last group is exposed
+    # data parallel: the flat gradient is all-reduced as dp.OverlappedGradReducer schedules it (VLB_DP_REDUCE: "deferred" = one
+    # all-reduce after the backward, "inline" = per finished chunk on the compute stream, "overlap" = per chunk on a side stream)
     reducer = dp.OverlappedGradReducer(device=dev, timing=True) if world > 1 else None
     eng.grad_ready = reducer
     if world > 1:
@@ -241,8 +241,9 @@ def run_ours(args):
         dp_info = {"allreduce_ms": round(float(allv[:, 2].max()), 3), "allreduce_exposed_ms": round(float(allv[:, 1].max()), 3),
                    "rank_skew_ms": round(float(allv[:, 0].max() - allv[:, 0].min()), 3),
                    "rank_compute_ms": [round(float(x), 2) for x in allv[:, 0]], "allreduce_bytes": 4 * eng.T.numel,
-                   "how": "allreduce_ms = sum of the chunked ncclAllReduce durations per step on the side stream (events, max over "
-                          "ranks); exposed = wait of the compute stream for the last chunk after the backward; rank_skew = max - "
+                   "schedule": reducer.mode,
+                   "how": "allreduce_ms = sum of the ncclAllReduce durations per step (CUDA events on the stream they run on, max "
+                          "over ranks); exposed = backward end -> gradients reduced, on the compute stream; rank_skew = max - "
                           "min over ranks of the step-start -> backward-end device time (3 extra steps)"}
 
     # ---- end-to-end arm through the public API with pinned host buffers (e2e)

@@ -8,6 +8,8 @@ The path has exactly two exchange steps:
     row count, then finalize on every rank (reference concatenates everything on one device, src/utils.py:101-106).
 Frozen weights are replicated and never communicated; clips are independent units.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -108,34 +110,65 @@ def make_sum_reducer(group=None):
 
 
 class OverlappedGradReducer:
-    """Engine.grad_ready target: all-reduces every finished slice of the flat gradient on a side stream while the backward of the
-    earlier decoder layers is still running ('launch per-chunk all-reduces as backward finishes each group of
-    layers'). `wait()` makes the compute stream wait for the last one; it must be called before the optimiser kernels."""
+    """Engine.grad_ready target: all-reduces every finished slice of the flat gradient ('launch per-chunk all-reduces as
+    backward finishes each group of layers'). `wait()` must be called before the optimiser kernels. Three schedules:
+      "overlap"   on a side stream while the backward of the earlier layers runs. Hides the transfer, but every GEMM of this library is
+                  a persistent kernel sized to ALL SMs with a static tile order: while NCCL's CTAs hold a few SMs the last GEMM CTAs
+                  start only when the first ones have finished their whole share -- on one 8-GPU box the step-start -> backward-end
+                  time went from 512 to 542 ms (profiles/r02an_*).
+      "inline"    on the compute stream, right where the slice becomes final: nothing runs beside NCCL, the ranks meet once per chunk.
+      "deferred"  (default) one all-reduce of the union of the slices inside wait(), i.e. after the whole backward."""
 
-    def __init__(self, group=None, device=None, timing=False):
+    def __init__(self, group=None, device=None, timing=False, mode=None):
         self.group, self.timing = group, timing
-        self.stream = torch.cuda.Stream(device)
-        self.spans = []                     # (start, end) events of each all-reduce on the side stream (timing=True)
+        self.mode = mode or os.environ.get("VLB_DP_REDUCE", "deferred")
+        assert self.mode in ("overlap", "inline", "deferred"), self.mode
+        self.stream = torch.cuda.Stream(device) if self.mode == "overlap" else None
+        self.spans = []                     # (start, end) events of each all-reduce (timing=True)
+        self.pending = []                   # deferred slices
         self.bytes = 0
+
+    def _reduce(self, t, stream):
+        if self.timing:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        if self.timing:
+            e1.record(stream)
+            self.spans.append((e0, e1))
+        self.bytes += t.numel() * t.element_size()
 
     def __call__(self, flat_slice):
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
             return
-        ready = torch.cuda.Event()
-        ready.record()                      # on the compute stream: everything that writes this slice has been enqueued
-        with torch.cuda.stream(self.stream):
-            self.stream.wait_event(ready)
-            if self.timing:
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record(self.stream)
-            dist.all_reduce(flat_slice, op=dist.ReduceOp.SUM, group=self.group)
-            if self.timing:
-                e1.record(self.stream)
-                self.spans.append((e0, e1))
-        self.bytes += flat_slice.numel() * flat_slice.element_size()
+        if self.mode == "deferred":
+            self.pending.append(flat_slice)
+        elif self.mode == "inline":
+            self._reduce(flat_slice, torch.cuda.current_stream())
+        else:
+            ready = torch.cuda.Event()
+            ready.record()                  # on the compute stream: everything that writes this slice has been enqueued
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(ready)
+                self._reduce(flat_slice, self.stream)
 
     def wait(self):
-        torch.cuda.current_stream().wait_stream(self.stream)
+        if self.mode == "overlap":
+            torch.cuda.current_stream().wait_stream(self.stream)
+        elif self.pending:
+            # the slices are pieces of one flat buffer: merge neighbours so that the usual case is a single all-reduce
+            parts = sorted(self.pending, key=lambda t: t.data_ptr())
+            self.pending = []
+            runs = [[parts[0]]]
+            for t in parts[1:]:
+                last = runs[-1][-1]
+                if last.data_ptr() + last.numel() * last.element_size() == t.data_ptr() and t.dtype == last.dtype:
+                    runs[-1].append(t)
+                else:
+                    runs.append([t])
+            for run in runs:
+                n = sum(t.numel() for t in run)
+                self._reduce(run[0].as_strided((n,), (1,)) if len(run) > 1 else run[0], torch.cuda.current_stream())
 
     def pop_ms(self):
         """Sum of the all-reduce durations recorded since the last call (synchronise first)."""
