@@ -20,18 +20,37 @@ constexpr int ATT_BM = 128;   // query rows per CTA
 constexpr int ATT_BN = 64;    // keys per inner block
 constexpr int ATT_THREADS = 256;
 
+#ifndef ATT_Q_TMEM
+#define ATT_Q_TMEM 0
+#endif
+// ATT_Q_TMEM (experiment, compiled out: correct -- all attention tests pass -- but SLOWER, causal d=128 682 vs 929 TF/s, ViT 338 vs
+// 416; profiles/r02aq_attn_*.jsonl): Q lives in TMEM (bf16 pairs, D/2 columns, written once by the softmax threads straight from global memory) and feeds
+// the QK MMA as a TMEM A operand. With both operands in shared memory an N=64 MMA fetches 4 KB of A + 2 KB of B per K=16 step, 48
+// cycles at 128 B/clk for 32 cycles of math; without the A fetch it is math-bound. TMEM then holds ONE S buffer (64) + Q (64) + O
+// (128) = 256 columns per CTA, so S(j+1) is issued behind PV(j) instead of two blocks ahead: inside a CTA the tensor and the
+// softmax phases alternate, and the SM's second CTA was meant to fill the other half of each. It does not: losing S(j+1) in
+// flight under softmax(j) costs more than the operand fetch saves.
 template <int D> struct AttCfg {
     static constexpr int Q_BYTES = ATT_BM * D * 2;
     static constexpr int KV_BYTES = ATT_BN * D * 2;
     static constexpr int P_BYTES = ATT_BM * ATT_BN * 2;
     static constexpr int K_STAGES = 3;                         // K is needed two key blocks ahead of V (S is issued two ahead)
+#if ATT_Q_TMEM
+    static constexpr int OFF_K = 0;                            // no Q tile in shared memory; the K ring doubles as the O staging tile
+    static constexpr int S_BUFS = 1;
+#else
     static constexpr int OFF_K = Q_BYTES;
+    static constexpr int S_BUFS = 2;
+#endif
     static constexpr int OFF_V = OFF_K + K_STAGES * KV_BYTES;
     static constexpr int OFF_BAR = OFF_V + 2 * KV_BYTES;      // P lives in TMEM: no staging buffer
     static constexpr int SMEM_BYTES = OFF_BAR + 256;          // + barriers; two CTAs fit one SM
-    static constexpr int TMEM_COLS = 256;                     // two S buffers (64 columns each) + O (D columns); x2 CTAs = 512
-    static constexpr int O_COL = 2 * ATT_BN;                  // S0 at column 0, S1 at 64, O after them
+    static constexpr int TMEM_COLS = 256;                     // S buffer(s) of 64 columns (+ Q) + O (D columns); x2 CTAs = 512
+    static constexpr int Q_COL = ATT_BN;                      // ATT_Q_TMEM: Q at columns [64, 64 + D/2)
+    static constexpr int O_COL = 2 * ATT_BN;                  // O after S (and S1 or Q)
 };
+static_assert(AttCfg<128>::K_STAGES * AttCfg<128>::KV_BYTES >= AttCfg<128>::Q_BYTES && AttCfg<64>::K_STAGES * AttCfg<64>::KV_BYTES >= AttCfg<64>::Q_BYTES,
+              "the K ring must hold the O staging tile");
 
 struct AttParams {
     int S;              // sequence length (rows per batch element)
@@ -41,6 +60,8 @@ struct AttParams {
     float* lse;         // [B, Hq, S] log2-domain logsumexp
     int Hq;
     long long* ts;      // debug (VLB_ATT_TS=1): clock64 stamps of the hand-offs of one heavy CTA, 8 per key block
+    const bf16* q;      // ATT_Q_TMEM: global Q [B*S, ldq] (head h at column h * D)
+    int ldq;
 };
 
 // P stays in TMEM. The softmax threads write bf16 P over the S buffer they just read (tcgen05.st) and the PV MMA takes
@@ -84,7 +105,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
         tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
     }
     if (warp == 1 && lane == 0) {
-        mbar_init(q_full, 1);
+        mbar_init(q_full, ATT_Q_TMEM ? 128 : 1);
         for (int i = 0; i < Cfg::K_STAGES; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
         mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(&p_ready[0], 128); mbar_init(&p_ready[1], 128); mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
@@ -98,9 +119,11 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
 
     if (warp == 0) {
         if (lane == 0) {
+#if !ATT_Q_TMEM
             mbar_expect_tx(q_full, Cfg::Q_BYTES);
 #pragma unroll
             for (int c = 0; c < D / 64; ++c) tma_load_3d(&tmQ, q_full, sQ + c * (ATT_BM * 128), h * D + c * 64, q0, b);
+#endif
             int ks = 0; uint32_t kph = 0;
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
@@ -130,13 +153,17 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 const int st = j & 1;
                 mbar_wait(&k_full[ks], kph);
                 tc_fence_after();
-                const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + ks * Cfg::KV_BYTES);
+                const uint32_t ka = smem_u32(sK + ks * Cfg::KV_BYTES);
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k) {
-                    const uint32_t off_q = (k >> 2) * (ATT_BM * 128) + (k & 3) * 32;
                     const uint32_t off_k = (k >> 2) * (ATT_BN * 128) + (k & 3) * 32;
-                    if (ldr) umma_bf16(tS + (uint32_t)(st * ATT_BN), make_smem_desc(qa + off_q, 0, 1024),
+#if ATT_Q_TMEM
+                    if (ldr) umma_bf16_ts(tS, tmem_base + Cfg::Q_COL + (uint32_t)(k * 8), make_smem_desc(ka + off_k, 0, 1024), idesc_qk, k > 0 ? 1u : 0u);
+#else
+                    const uint32_t off_q = (k >> 2) * (ATT_BM * 128) + (k & 3) * 32;
+                    if (ldr) umma_bf16(tS + (uint32_t)(st * ATT_BN), make_smem_desc(smem_u32(sQ) + off_q, 0, 1024),
                                        make_smem_desc(ka + off_k, 0, 1024), idesc_qk, k > 0 ? 1u : 0u);
+#endif
                 }
                 if (ldr) { umma_commit(&k_empty[ks]); umma_commit(&s_full[st]); }
                 __syncwarp();
@@ -145,8 +172,9 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             // S is double-buffered in TMEM and issued two key blocks ahead, so the tensor pipe computes S(j+1) while the
             // softmax threads are still working on S(j); PV(j) (on the critical path to the next P write) goes first.
             mbar_wait(q_full, 0);
+            tc_fence_after();
             issue_qk(0);
-            if (nblk > 1) issue_qk(1);
+            if (Cfg::S_BUFS == 2 && nblk > 1) issue_qk(1);
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1;
                 mbar_wait(&p_ready[j & 1], (j >> 1) & 1);  // P(j) in TMEM (over S buffer j & 1)
@@ -159,13 +187,13 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
 #pragma unroll
                 for (int k = 0; k < ATT_BN / 16; ++k) {
                     // A = P [128 x 64] from TMEM (bf16 pairs, 8 columns per K=16); B = V tile [64 keys x D], MN-major operand
-                    if (ldr) umma_bf16_ts(tO, tS + (uint32_t)(st * ATT_BN + k * 8),
+                    if (ldr) umma_bf16_ts(tO, tS + (uint32_t)((Cfg::S_BUFS == 2 ? st * ATT_BN : 0) + k * 8),
                                           make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
                 }
                 if (ldr) { umma_commit(&v_empty[st]); umma_commit(&pv_done[j & 1]); }
                 __syncwarp();
                 if (ldr) ATT_TS(6);
-                if (j + 2 < nblk) issue_qk(j + 2);
+                if (j + Cfg::S_BUFS < nblk) issue_qk(j + Cfg::S_BUFS);   // in order behind PV(j), which reads P from the buffer this S overwrites
                 if (ldr) ATT_TS(7);
             }
         }
@@ -176,13 +204,32 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
         const uint32_t tS = tmem_base + lane_off, tO = tmem_base + lane_off + Cfg::O_COL;
         const int qrow = q0 + row;
         float m_used = -INFINITY, l = 0.f;
+#if ATT_Q_TMEM
+        {   // this thread's query row, already packed as the bf16 pairs the TMEM A operand wants
+            const uint4* qg = reinterpret_cast<const uint4*>(p.q + ((size_t)b * p.S + qrow) * p.ldq + h * D);
+#pragma unroll
+            for (int c0 = 0; c0 < D / 2; c0 += 32) {
+                uint32_t qr[32];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const uint4 v = qrow < p.S ? __ldg(qg + c0 / 4 + c) : make_uint4(0u, 0u, 0u, 0u);
+                    qr[c * 4] = v.x; qr[c * 4 + 1] = v.y; qr[c * 4 + 2] = v.z; qr[c * 4 + 3] = v.w;
+                }
+                tmem_st32(tmem_base + lane_off + Cfg::Q_COL + c0, qr);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(q_full);
+        }
+#endif
+        constexpr int SB = Cfg::S_BUFS == 2 ? ATT_BN : 0;     // column distance between the S buffers
         for (int j = 0; j < nblk; ++j) {
             mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             tc_fence_after();
             if (warp == 4) ATT_TS(0);
             uint32_t r0[32], r1[32];
-            tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN), r0);
-            tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN) + 32, r1);
+            tmem_ld32(tS + (uint32_t)((j & 1) * SB), r0);
+            tmem_ld32(tS + (uint32_t)((j & 1) * SB) + 32, r1);
             tmem_ld_wait();
             if (warp == 4) ATT_TS(1);
             // raw scores: the softmax scale is folded into the exponent's FMA (max commutes with the positive scale)
@@ -241,7 +288,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             }
             l += sum;
             if (warp == 4) ATT_TS(2);
-            tmem_st32(tS + (uint32_t)((j & 1) * ATT_BN), pk);
+            tmem_st32(tS + (uint32_t)((j & 1) * SB), pk);
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(&p_ready[j & 1]);
@@ -318,6 +365,7 @@ static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_q
     AttParams p;
     p.S = S; p.kv_len = S; p.group = Hq / Hkv; p.scale_log2 = scale * 1.4426950408889634f; p.lse = lse; p.Hq = Hq;
     p.ts = att_ts_buffer();
+    p.q = reinterpret_cast<const bf16*>(q); p.ldq = ld_qkv;
     auto kern = attn_fwd_kernel<D, CAUSAL>;
     static bool attr = false;
     if (!attr) {
