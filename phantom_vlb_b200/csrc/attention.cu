@@ -67,6 +67,24 @@ struct AttParams {
 // P stays in TMEM. The softmax threads write bf16 P over the S buffer they just read (tcgen05.st) and the PV MMA takes
 // its A operand from TMEM, so P never crosses shared memory (-32 of the 128 KB of smem traffic per key block; the kernel is
 // shared-memory-bandwidth bound) and P(j) no longer has to wait for PV(j-1) to release a staging buffer.
+// exp2 on the FMA pipe for a share of the exponentials (experiment, off): the idea was that the softmax phase is bound by the XU (64 ex2
+// per thread and key block, 8 cycles each per warp, the SM's two CTAs sharing every sub-partition's XU) with FMA slots to spare. Round-to-nearest split
+// x = n + f, f in [-0.5, 0.5]; 2^f by its degree-4 Taylor polynomial (relative error < 5e-5, far below the bf16 rounding of P, 2e-3);
+// 2^n goes into the exponent field; below 2^-126 (masked scores are -inf) the result is 0.
+#ifndef ATT_EXP2_POLY
+#define ATT_EXP2_POLY 0          // of every 8 exponentials, this many are evaluated as polynomials. Measured: 0 -> 932 TF/s, 2 -> 655,
+                                 // 3 -> 574 (profiles/r02ar_attn_poly.log): the softmax is bound by issue slots, not by the XU
+#endif
+__device__ __forceinline__ float exp2_poly(float x) {
+    const float xc = fmaxf(x, -126.f);
+    const float t = xc + 12582912.f;                      // 1.5 * 2^23: the low mantissa bits of t hold rint(x)
+    const float f = xc - (t - 12582912.f);
+    float p = fmaf(f, 0.00961812910762848f, 0.0555041086648216f);
+    p = fmaf(p, f, 0.240226506959101f);
+    p = fmaf(p, f, 0.693147180559945f);
+    p = fmaf(p, f, 1.0f);
+    return x < -126.f ? 0.f : __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
 #define ATT_TS(slot) do { if (ts_on) p.ts[j * 8 + (slot)] = clock64(); } while (0)
 template <int D, bool CAUSAL>
 __global__ void __launch_bounds__(ATT_THREADS, 2)
@@ -280,7 +298,10 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             for (int c8 = 0; c8 < 8; ++c8) {
                 float e[8];
 #pragma unroll
-                for (int t = 0; t < 8; ++t) { e[t] = exp2f(fmaf(s[c8 * 8 + t], p.scale_log2, neg_m)); }
+                for (int t = 0; t < 8; ++t) {
+                    const float x = fmaf(s[c8 * 8 + t], p.scale_log2, neg_m);
+                    e[t] = t < ATT_EXP2_POLY ? exp2_poly(x) : exp2f(x);
+                }
                 uint4 u;
                 u.x = pack_bf16(e[0], e[1]); u.y = pack_bf16(e[2], e[3]); u.z = pack_bf16(e[4], e[5]); u.w = pack_bf16(e[6], e[7]);
                 sum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));      // fp32 row sum (as flash-attn)
