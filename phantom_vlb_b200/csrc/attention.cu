@@ -291,22 +291,23 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 l *= f;
                 m_used = m_new;
             }
-            float sum = 0.f;
-            const float neg_m = -m_used;
+            // packed fp32 (FFMA2 / FADD2, sm_100): the softmax threads are bound by issue slots, and the exponent's FMA and the row sum
+            // are two of the ~4.5 instructions per score
+            float2 sum2 = make_float2(0.f, 0.f);
+            const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(-m_used, -m_used);
             uint32_t pk[32];                                  // PT: the row's 64 probabilities as bf16 pairs
 #pragma unroll
-            for (int c8 = 0; c8 < 8; ++c8) {
-                float e[8];
-#pragma unroll
-                for (int t = 0; t < 8; ++t) {
-                    const float x = fmaf(s[c8 * 8 + t], p.scale_log2, neg_m);
-                    e[t] = t < ATT_EXP2_POLY ? exp2_poly(x) : exp2f(x);
-                }
-                uint4 u;
-                u.x = pack_bf16(e[0], e[1]); u.y = pack_bf16(e[2], e[3]); u.z = pack_bf16(e[4], e[5]); u.w = pack_bf16(e[6], e[7]);
-                sum += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));      // fp32 row sum (as flash-attn)
-                pk[c8 * 4] = u.x; pk[c8 * 4 + 1] = u.y; pk[c8 * 4 + 2] = u.z; pk[c8 * 4 + 3] = u.w;
+            for (int c2 = 0; c2 < 32; ++c2) {
+                const float2 x = __ffma2_rn(make_float2(s[2 * c2], s[2 * c2 + 1]), sc2, nm2);
+#if ATT_EXP2_POLY
+                const float2 e = make_float2((c2 & 3) * 2 < ATT_EXP2_POLY ? exp2_poly(x.x) : exp2f(x.x), (c2 & 3) * 2 + 1 < ATT_EXP2_POLY ? exp2_poly(x.y) : exp2f(x.y));
+#else
+                const float2 e = make_float2(exp2f(x.x), exp2f(x.y));
+#endif
+                sum2 = __fadd2_rn(sum2, e);                   // fp32 row sum (as flash-attn)
+                pk[c2] = pack_bf16(e.x, e.y);
             }
+            const float sum = sum2.x + sum2.y;
             l += sum;
             if (warp == 4) ATT_TS(2);
             tmem_st32(tS + (uint32_t)((j & 1) * SB), pk);
