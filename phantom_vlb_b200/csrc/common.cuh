@@ -117,6 +117,41 @@ __device__ __forceinline__ void det_grid_add(DetSumWs& ws, float s /* valid in t
 }
 
 // ---------------------------------------------------------------- activations
+// v[i] = float(bf16(s * v[i])) for 8 values: packed multiply, one packed convert per pair, the bf16 halves moved back up by shifts
+__device__ __forceinline__ void scale_round_bf16_8(float (&v)[8], float s) {
+    const float2 s2 = make_float2(s, s);
+#pragma unroll
+    for (int j = 0; j < 8; j += 2) {
+        const float2 m = __fmul2_rn(make_float2(v[j], v[j + 1]), s2);
+        const uint32_t u = pack_bf16(m.x, m.y);
+        v[j] = __uint_as_float(u << 16);
+        v[j + 1] = __uint_as_float(u & 0xFFFF0000u);
+    }
+}
+__device__ __forceinline__ float rcp_approx(float x) {           // what 1.f / x compiles to under --use_fast_math (MUFU.RCP)
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// SwiGLU backward of 8 features, shared by the stand-alone kernel and the GEMM epilogues (which must agree bit for bit):
+//   dg = (d u) (sg (1 + g (1 - sg))),  du = d (g sg),  sg = sigmoid(g), with the fp32 arithmetic issued as packed pairs (FMUL2 / FFMA2 /
+// FADD2, sm_100): 6.5 instead of 11 arithmetic instructions per feature in epilogues that sit right at the length of a K = 4096 main loop.
+__device__ __forceinline__ void swiglu_bwd8(const float (&g)[8], const float (&u)[8], const float (&d)[8], float (&dg)[8], float (&du)[8]) {
+    const float2 one2 = make_float2(1.f, 1.f), m1 = make_float2(-1.f, -1.f), nl2e = make_float2(-1.4426950408889634f, -1.4426950408889634f);
+#pragma unroll
+    for (int j = 0; j < 8; j += 2) {
+        const float2 g2 = make_float2(g[j], g[j + 1]);
+        const float2 a = __fmul2_rn(g2, nl2e);
+        const float2 den = __fadd2_rn(make_float2(exp2f(a.x), exp2f(a.y)), one2);
+        const float2 sg = make_float2(rcp_approx(den.x), rcp_approx(den.y));
+        const float2 d2 = make_float2(d[j], d[j + 1]);
+        const float2 du2 = __fmul2_rn(d2, __fmul2_rn(g2, sg));
+        const float2 om = __ffma2_rn(sg, m1, one2);                   // 1 - sg
+        const float2 t = __fmul2_rn(sg, __ffma2_rn(g2, om, one2));    // sg (1 + g (1 - sg))
+        const float2 dg2 = __fmul2_rn(__fmul2_rn(d2, make_float2(u[j], u[j + 1])), t);
+        dg[j] = dg2.x; dg[j + 1] = dg2.y; du[j] = du2.x; du[j + 1] = du2.y;
+    }
+}
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
 __device__ __forceinline__ float siluf_(float x) { return x * sigmoidf_(x); }
 // x * sigmoid(1.702 x) with sigmoid(t) = 0.5 + 0.5 tanh(t / 2): ONE MUFU op (tanh.approx, rel. error ~2^-11, far below the bf16

@@ -313,12 +313,8 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r8[j]) * p.alpha;
                         lora_rank16_add8_slots(dv, tf[0], b0, b1, smem_u32(cdg), q, lane, ch, (unsigned int)(kw >> (ch * 8)) & 0xFFu, p.lr_scale);
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float d = bf2f(f2bf(dv[j]));
-                            const float sg = 1.f / (1.f + __expf(-g[j]));
-                            du[j] = d * (g[j] * sg);
-                            dg[j] = d * u[j] * (sg * (1.f + g[j] * (1.f - sg)));
-                        }
+                        for (int j = 0; j < 8; ++j) dv[j] = bf2f(f2bf(dv[j]));            // d(act) as the unfused path stores it
+                        swiglu_bwd8(g, u, dv, dg, du);
                         uint4 vg, vu;
                         vg.x = pack_bf16(dg[0], dg[1]); vg.y = pack_bf16(dg[2], dg[3]); vg.z = pack_bf16(dg[4], dg[5]); vg.w = pack_bf16(dg[6], dg[7]);
                         vu.x = pack_bf16(du[0], du[1]); vu.y = pack_bf16(du[2], du[3]); vu.z = pack_bf16(du[4], du[5]); vu.w = pack_bf16(du[6], du[7]);
@@ -371,15 +367,9 @@ gemm2_tcgen05_kernel(const GemmParams p,
                             float g[8], u[8], dg[8], du[8], dv[8];
                             unpack8(gv[c], g); unpack8(uv[c], u);
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const float d = bf2f(f2bf(dv[j]));                                     // d(act) as the unfused path stores it
-                                const float sg = 1.f / (1.f + __expf(-g[j]));
-                                const float si = g[j] * sg;
-                                du[j] = d * si;
-                                dg[j] = d * u[j] * (sg * (1.f + g[j] * (1.f - sg)));
-                            }
+                            for (int j = 0; j < 8; ++j) dv[j] = __uint_as_float(r[c * 8 + j]);
+                            scale_round_bf16_8(dv, p.alpha);                              // d(act) as the unfused path stores it
+                            swiglu_bwd8(g, u, dv, dg, du);
                             uint4 vg, vu;
                             vg.x = pack_bf16(dg[0], dg[1]); vg.y = pack_bf16(dg[2], dg[3]); vg.z = pack_bf16(dg[4], dg[5]); vg.w = pack_bf16(dg[6], dg[7]);
                             vu.x = pack_bf16(du[0], du[1]); vu.y = pack_bf16(du[2], du[3]); vu.z = pack_bf16(du[4], du[5]); vu.w = pack_bf16(du[6], du[7]);

@@ -287,13 +287,7 @@ __global__ void swiglu_bwd_kernel(const bf16* __restrict__ gu, const bf16* __res
         load8(gu + row * 2 * I + c * 8, g);
         load8(gu + row * 2 * I + I + c * 8, u);
         load8(dact + row * I + c * 8, d);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float sg = 1.f / (1.f + __expf(-g[j]));
-            const float si = g[j] * sg;
-            du[j] = d[j] * si;
-            dg[j] = d[j] * u[j] * (sg * (1.f + g[j] * (1.f - sg)));
-        }
+        swiglu_bwd8(g, u, d, dg, du);
         store8(dgu + row * 2 * I + c * 8, dg);
         store8(dgu + row * 2 * I + I + c * 8, du);
     }
