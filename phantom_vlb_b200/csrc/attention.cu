@@ -20,37 +20,18 @@ constexpr int ATT_BM = 128;   // query rows per CTA
 constexpr int ATT_BN = 64;    // keys per inner block
 constexpr int ATT_THREADS = 256;
 
-#ifndef ATT_Q_TMEM
-#define ATT_Q_TMEM 0
-#endif
-// ATT_Q_TMEM (experiment, compiled out: correct -- all attention tests pass -- but SLOWER, causal d=128 682 vs 929 TF/s, ViT 338 vs
-// 416; profiles/r02aq_attn_*.jsonl): Q lives in TMEM (bf16 pairs, D/2 columns, written once by the softmax threads straight from global memory) and feeds
-// the QK MMA as a TMEM A operand. With both operands in shared memory an N=64 MMA fetches 4 KB of A + 2 KB of B per K=16 step, 48
-// cycles at 128 B/clk for 32 cycles of math; without the A fetch it is math-bound. TMEM then holds ONE S buffer (64) + Q (64) + O
-// (128) = 256 columns per CTA, so S(j+1) is issued behind PV(j) instead of two blocks ahead: inside a CTA the tensor and the
-// softmax phases alternate, and the SM's second CTA was meant to fill the other half of each. It does not: losing S(j+1) in
-// flight under softmax(j) costs more than the operand fetch saves.
 template <int D> struct AttCfg {
     static constexpr int Q_BYTES = ATT_BM * D * 2;
     static constexpr int KV_BYTES = ATT_BN * D * 2;
     static constexpr int P_BYTES = ATT_BM * ATT_BN * 2;
     static constexpr int K_STAGES = 3;                         // K is needed two key blocks ahead of V (S is issued two ahead)
-#if ATT_Q_TMEM
-    static constexpr int OFF_K = 0;                            // no Q tile in shared memory; the K ring doubles as the O staging tile
-    static constexpr int S_BUFS = 1;
-#else
     static constexpr int OFF_K = Q_BYTES;
-    static constexpr int S_BUFS = 2;
-#endif
     static constexpr int OFF_V = OFF_K + K_STAGES * KV_BYTES;
     static constexpr int OFF_BAR = OFF_V + 2 * KV_BYTES;      // P lives in TMEM: no staging buffer
     static constexpr int SMEM_BYTES = OFF_BAR + 256;          // + barriers; two CTAs fit one SM
-    static constexpr int TMEM_COLS = 256;                     // S buffer(s) of 64 columns (+ Q) + O (D columns); x2 CTAs = 512
-    static constexpr int Q_COL = ATT_BN;                      // ATT_Q_TMEM: Q at columns [64, 64 + D/2)
-    static constexpr int O_COL = 2 * ATT_BN;                  // O after S (and S1 or Q)
+    static constexpr int TMEM_COLS = 256;                     // two S buffers (64 columns each) + O (D columns); x2 CTAs = 512
+    static constexpr int O_COL = 2 * ATT_BN;                  // S0 at column 0, S1 at 64, O after them
 };
-static_assert(AttCfg<128>::K_STAGES * AttCfg<128>::KV_BYTES >= AttCfg<128>::Q_BYTES && AttCfg<64>::K_STAGES * AttCfg<64>::KV_BYTES >= AttCfg<64>::Q_BYTES,
-              "the K ring must hold the O staging tile");
 
 struct AttParams {
     int S;              // sequence length (rows per batch element)
@@ -60,31 +41,11 @@ struct AttParams {
     float* lse;         // [B, Hq, S] log2-domain logsumexp
     int Hq;
     long long* ts;      // debug (VLB_ATT_TS=1): clock64 stamps of the hand-offs of one heavy CTA, 8 per key block
-    const bf16* q;      // ATT_Q_TMEM: global Q [B*S, ldq] (head h at column h * D)
-    int ldq;
 };
 
 // P stays in TMEM. The softmax threads write bf16 P over the S buffer they just read (tcgen05.st) and the PV MMA takes
 // its A operand from TMEM, so P never crosses shared memory (-32 of the 128 KB of smem traffic per key block; the kernel is
 // shared-memory-bandwidth bound) and P(j) no longer has to wait for PV(j-1) to release a staging buffer.
-// exp2 on the FMA pipe for a share of the exponentials (experiment, off): the idea was that the softmax phase is bound by the XU (64 ex2
-// per thread and key block, 8 cycles each per warp, the SM's two CTAs sharing every sub-partition's XU) with FMA slots to spare. Round-to-nearest split
-// x = n + f, f in [-0.5, 0.5]; 2^f by its degree-4 Taylor polynomial (relative error < 5e-5, far below the bf16 rounding of P, 2e-3);
-// 2^n goes into the exponent field; below 2^-126 (masked scores are -inf) the result is 0.
-#ifndef ATT_EXP2_POLY
-#define ATT_EXP2_POLY 0          // of every 8 exponentials, this many are evaluated as polynomials. Measured: 0 -> 932 TF/s, 2 -> 655,
-                                 // 3 -> 574 (profiles/r02ar_attn_poly.log): the softmax is bound by issue slots, not by the XU
-#endif
-__device__ __forceinline__ float exp2_poly(float x) {
-    const float xc = fmaxf(x, -126.f);
-    const float t = xc + 12582912.f;                      // 1.5 * 2^23: the low mantissa bits of t hold rint(x)
-    const float f = xc - (t - 12582912.f);
-    float p = fmaf(f, 0.00961812910762848f, 0.0555041086648216f);
-    p = fmaf(p, f, 0.240226506959101f);
-    p = fmaf(p, f, 0.693147180559945f);
-    p = fmaf(p, f, 1.0f);
-    return x < -126.f ? 0.f : __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
 #define ATT_TS(slot) do { if (ts_on) p.ts[j * 8 + (slot)] = clock64(); } while (0)
 template <int D, bool CAUSAL>
 __global__ void __launch_bounds__(ATT_THREADS, 2)
@@ -123,7 +84,7 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
         tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
     }
     if (warp == 1 && lane == 0) {
-        mbar_init(q_full, ATT_Q_TMEM ? 128 : 1);
+        mbar_init(q_full, 1);
         for (int i = 0; i < Cfg::K_STAGES; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
         mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(&p_ready[0], 128); mbar_init(&p_ready[1], 128); mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
@@ -137,11 +98,9 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
 
     if (warp == 0) {
         if (lane == 0) {
-#if !ATT_Q_TMEM
             mbar_expect_tx(q_full, Cfg::Q_BYTES);
 #pragma unroll
             for (int c = 0; c < D / 64; ++c) tma_load_3d(&tmQ, q_full, sQ + c * (ATT_BM * 128), h * D + c * 64, q0, b);
-#endif
             int ks = 0; uint32_t kph = 0;
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
@@ -171,17 +130,13 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 const int st = j & 1;
                 mbar_wait(&k_full[ks], kph);
                 tc_fence_after();
-                const uint32_t ka = smem_u32(sK + ks * Cfg::KV_BYTES);
+                const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + ks * Cfg::KV_BYTES);
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k) {
-                    const uint32_t off_k = (k >> 2) * (ATT_BN * 128) + (k & 3) * 32;
-#if ATT_Q_TMEM
-                    if (ldr) umma_bf16_ts(tS, tmem_base + Cfg::Q_COL + (uint32_t)(k * 8), make_smem_desc(ka + off_k, 0, 1024), idesc_qk, k > 0 ? 1u : 0u);
-#else
                     const uint32_t off_q = (k >> 2) * (ATT_BM * 128) + (k & 3) * 32;
-                    if (ldr) umma_bf16(tS + (uint32_t)(st * ATT_BN), make_smem_desc(smem_u32(sQ) + off_q, 0, 1024),
+                    const uint32_t off_k = (k >> 2) * (ATT_BN * 128) + (k & 3) * 32;
+                    if (ldr) umma_bf16(tS + (uint32_t)(st * ATT_BN), make_smem_desc(qa + off_q, 0, 1024),
                                        make_smem_desc(ka + off_k, 0, 1024), idesc_qk, k > 0 ? 1u : 0u);
-#endif
                 }
                 if (ldr) { umma_commit(&k_empty[ks]); umma_commit(&s_full[st]); }
                 __syncwarp();
@@ -190,9 +145,8 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
             // S is double-buffered in TMEM and issued two key blocks ahead, so the tensor pipe computes S(j+1) while the
             // softmax threads are still working on S(j); PV(j) (on the critical path to the next P write) goes first.
             mbar_wait(q_full, 0);
-            tc_fence_after();
             issue_qk(0);
-            if (Cfg::S_BUFS == 2 && nblk > 1) issue_qk(1);
+            if (nblk > 1) issue_qk(1);
             for (int j = 0; j < nblk; ++j) {
                 const int st = j & 1;
                 mbar_wait(&p_ready[j & 1], (j >> 1) & 1);  // P(j) in TMEM (over S buffer j & 1)
@@ -205,13 +159,13 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
 #pragma unroll
                 for (int k = 0; k < ATT_BN / 16; ++k) {
                     // A = P [128 x 64] from TMEM (bf16 pairs, 8 columns per K=16); B = V tile [64 keys x D], MN-major operand
-                    if (ldr) umma_bf16_ts(tO, tS + (uint32_t)((Cfg::S_BUFS == 2 ? st * ATT_BN : 0) + k * 8),
+                    if (ldr) umma_bf16_ts(tO, tS + (uint32_t)(st * ATT_BN + k * 8),
                                           make_smem_desc(va + k * (16 * 128), ATT_BN * 128, 1024), idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
                 }
                 if (ldr) { umma_commit(&v_empty[st]); umma_commit(&pv_done[j & 1]); }
                 __syncwarp();
                 if (ldr) ATT_TS(6);
-                if (j + Cfg::S_BUFS < nblk) issue_qk(j + Cfg::S_BUFS);   // in order behind PV(j), which reads P from the buffer this S overwrites
+                if (j + 2 < nblk) issue_qk(j + 2);
                 if (ldr) ATT_TS(7);
             }
         }
@@ -222,32 +176,13 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
         const uint32_t tS = tmem_base + lane_off, tO = tmem_base + lane_off + Cfg::O_COL;
         const int qrow = q0 + row;
         float m_used = -INFINITY, l = 0.f;
-#if ATT_Q_TMEM
-        {   // this thread's query row, already packed as the bf16 pairs the TMEM A operand wants
-            const uint4* qg = reinterpret_cast<const uint4*>(p.q + ((size_t)b * p.S + qrow) * p.ldq + h * D);
-#pragma unroll
-            for (int c0 = 0; c0 < D / 2; c0 += 32) {
-                uint32_t qr[32];
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    const uint4 v = qrow < p.S ? __ldg(qg + c0 / 4 + c) : make_uint4(0u, 0u, 0u, 0u);
-                    qr[c * 4] = v.x; qr[c * 4 + 1] = v.y; qr[c * 4 + 2] = v.z; qr[c * 4 + 3] = v.w;
-                }
-                tmem_st32(tmem_base + lane_off + Cfg::Q_COL + c0, qr);
-            }
-            tmem_st_wait();
-            tc_fence_before();
-            mbar_arrive(q_full);
-        }
-#endif
-        constexpr int SB = Cfg::S_BUFS == 2 ? ATT_BN : 0;     // column distance between the S buffers
         for (int j = 0; j < nblk; ++j) {
             mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             tc_fence_after();
             if (warp == 4) ATT_TS(0);
             uint32_t r0[32], r1[32];
-            tmem_ld32(tS + (uint32_t)((j & 1) * SB), r0);
-            tmem_ld32(tS + (uint32_t)((j & 1) * SB) + 32, r1);
+            tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN), r0);
+            tmem_ld32(tS + (uint32_t)((j & 1) * ATT_BN) + 32, r1);
             tmem_ld_wait();
             if (warp == 4) ATT_TS(1);
             // raw scores: the softmax scale is folded into the exponent's FMA (max commutes with the positive scale)
@@ -291,26 +226,23 @@ attn_fwd_kernel(const AttParams p, const __grid_constant__ CUtensorMap tmQ, cons
                 l *= f;
                 m_used = m_new;
             }
-            // packed fp32 (FFMA2 / FADD2, sm_100): the softmax threads are bound by issue slots, and the exponent's FMA and the row sum
-            // are two of the ~4.5 instructions per score
+            // packed fp32 (FFMA2 / FADD2, sm_100) for the exponent's FMA and the row sum. Two experiments of this round are NOT here
+            // because they were slower (profiles/r02aq_*, r02ar_*): Q as a TMEM A operand with a single S buffer
+            // (682 vs 929 TF/s) and part of the exponentials as polynomials on the FMA pipe (655 with 2 of 8).
             float2 sum2 = make_float2(0.f, 0.f);
             const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), nm2 = make_float2(-m_used, -m_used);
             uint32_t pk[32];                                  // PT: the row's 64 probabilities as bf16 pairs
 #pragma unroll
             for (int c2 = 0; c2 < 32; ++c2) {
                 const float2 x = __ffma2_rn(make_float2(s[2 * c2], s[2 * c2 + 1]), sc2, nm2);
-#if ATT_EXP2_POLY
-                const float2 e = make_float2((c2 & 3) * 2 < ATT_EXP2_POLY ? exp2_poly(x.x) : exp2f(x.x), (c2 & 3) * 2 + 1 < ATT_EXP2_POLY ? exp2_poly(x.y) : exp2f(x.y));
-#else
                 const float2 e = make_float2(exp2f(x.x), exp2f(x.y));
-#endif
                 sum2 = __fadd2_rn(sum2, e);                   // fp32 row sum (as flash-attn)
                 pk[c2] = pack_bf16(e.x, e.y);
             }
             const float sum = sum2.x + sum2.y;
             l += sum;
             if (warp == 4) ATT_TS(2);
-            tmem_st32(tS + (uint32_t)((j & 1) * SB), pk);
+            tmem_st32(tS + (uint32_t)((j & 1) * ATT_BN), pk);
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(&p_ready[j & 1]);
@@ -387,7 +319,6 @@ static int launch_attn_fwd(const void* q, const void* k, const void* v, int ld_q
     AttParams p;
     p.S = S; p.kv_len = S; p.group = Hq / Hkv; p.scale_log2 = scale * 1.4426950408889634f; p.lse = lse; p.Hq = Hq;
     p.ts = att_ts_buffer();
-    p.q = reinterpret_cast<const bf16*>(q); p.ldq = ld_qkv;
     auto kern = attn_fwd_kernel<D, CAUSAL>;
     static bool attr = false;
     if (!attr) {
