@@ -39,8 +39,6 @@ __device__ __forceinline__ unsigned int hash32(unsigned int x, unsigned int k1, 
 // decided as soon as its bit differs from thresh's), which leaves 64 / 2^DB_PLANES = 1 lane per word undecided on average;
 // those draw their remaining 32 - DB_PLANES bits from one more hash each. The drop probability is exactly thresh / 2^32.
 // (Running the planes until the whole warp is decided costs the MAXIMUM over 2048 lanes, ~12 planes; this costs 6 + a tail.)
-// 128 threads x 18 registers per block: small enough to sit beside a 384-thread pair-GEMM CTA on the same SM, so the masks of
-// a step can be generated on a side stream underneath the tensor-core kernels (Engine._pregen_masks).
 constexpr int DB_PLANES = 6;
 constexpr int DB_THREADS = 128;
 __global__ void __launch_bounds__(DB_THREADS) dropout_bits_kernel(unsigned long long* __restrict__ bits, long long nwords,

@@ -32,8 +32,6 @@ class Engine:
         # is ever written); other ranks fall back to materialised dropout(x) + a rank-r GEMM + masked add per projection input.
         self.lora_dropout = float(lora_dropout or 0.0)
         self.masked_lora = cfg.lora_r == 16 and os.environ.get("VLB_LORA_MASKED", "1") != "0"
-        self.pregen_masks = os.environ.get("VLB_PREGEN_MASKS", "0") == "1"      # measured: no gain (tools/ab_dropout.py), off by default
-        self.mask_stream, self.mask_events, self._pregen = None, None, None
         self.drop_bits = None       # test hook: dict filled with the packed keep masks keyed by (layer, site)
         self.drop_step = 0
         self.seed_mix = 0           # set_seed(seed, rank): every data-parallel rank draws its own dropout masks
@@ -230,33 +228,11 @@ class Engine:
                 self.drop_bits[(l, site)] = bits
         return [bits[a] for a in range(n_ad)]
 
-    def _pregen_masks(self, M):
-        """Every keep mask of this step (7 adapters x layers, 1 bit per element) generated NOW on a side stream: the masks depend
-        on (seed, step, layer, adapter) only, the generator is ALU-bound and its 128-thread blocks fit beside a pair-GEMM CTA on
-        the same SM, so it runs underneath the vision tower and the first decoder layers instead of in front of each layer's
-        GEMMs. Layer l's forward waits for event l. The buffers are this step's own from here to the end of its backward."""
-        cfg = self.cfg
-        if self.mask_stream is None:
-            self.mask_stream = torch.cuda.Stream(device=self.dev)
-            self.mask_events = [torch.cuda.Event() for _ in range(cfg.layers)]
-        main = torch.cuda.current_stream()
-        self.mask_stream.wait_stream(main)              # the previous step's backward has consumed the old masks
-        H, I = cfg.hidden, cfg.mlp
-        with torch.cuda.stream(self.mask_stream):
-            for l in range(cfg.layers):
-                for site, n_ad, K in ((0, 3, H), (1, 1, H), (2, 2, H), (3, 1, I)):
-                    self._site_bits(l, site, n_ad, M, K, True)
-                self.mask_events[l].record(self.mask_stream)
-        self._pregen = (self.drop_step, M)
-
     def _lora_down(self, x, A, xa, l, site, training):
         """xa = s * dropout(x) A^T for the adapters of one projection input (forward)."""
         n_ad = A.shape[0] // self.cfg.lora_r
         if self._masked(training):
-            pre = self._pregen == (self.drop_step, x.shape[0])
-            if pre and site == 0:
-                torch.cuda.current_stream().wait_event(self.mask_events[l])
-            bits = self._site_bits(l, site, n_ad, x.shape[0], x.shape[1], not pre)
+            bits = self._site_bits(l, site, n_ad, x.shape[0], x.shape[1], True)
             ops.lora_down_masked(x, A, xa, bits, self.scale / (1.0 - self.lora_dropout))
             self.launches += 1
             return
@@ -565,8 +541,6 @@ class Engine:
         B = batch["vision"].shape[0]
         lora = self.cfg.use_lora
         self.drop_step += 1          # fresh LoRA dropout masks every training step (same masks in its backward)
-        if lora and self._masked() and self.pregen_masks:
-            self._pregen_masks(B * self.cfg.max_len)
         self._zero_grads()
         hidden, wm = self.backbone_forward(batch, save=lora)
         self.hidden_pre_norm = hidden
