@@ -144,7 +144,7 @@ class OverlappedGradReducer:
         if self.mode == "deferred":
             self.pending.append(flat_slice)
         elif self.mode == "inline":
-            self._reduce(flat_slice, torch.cuda.current_stream())
+            self._reduce(flat_slice, self._cur())
         else:
             ready = torch.cuda.Event()
             ready.record()                  # on the compute stream: everything that writes this slice has been enqueued
@@ -168,7 +168,10 @@ class OverlappedGradReducer:
                     runs.append([t])
             for run in runs:
                 n = sum(t.numel() for t in run)
-                self._reduce(run[0].as_strided((n,), (1,)) if len(run) > 1 else run[0], torch.cuda.current_stream())
+                self._reduce(run[0].as_strided((n,), (1,)) if len(run) > 1 else run[0], self._cur())
+
+    def _cur(self):
+        return torch.cuda.current_stream() if self.timing else None      # only the timing events need the stream (gloo tests have none)
 
     def pop_ms(self):
         """Sum of the all-reduce durations recorded since the last call (synchronise first)."""

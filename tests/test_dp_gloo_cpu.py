@@ -85,6 +85,32 @@ def _worker(rank, world, port, q):
         sq = torch.tensor([float((gW ** 2).sum())], dtype=torch.float64)
         reduce(sq)
         assert abs(float(sq) - float((W.grad ** 2).sum())) < 1e-9
+        # ---- the engine's gradient hook: slices of one flat buffer handed over out of order (head first, then layer groups from
+        # the top down) are reduced as ONE all-reduce after the backward ("deferred"), or one by one where they become final ("inline")
+        calls = []
+        real = dist.all_reduce
+
+        def counting(t, *a, **k):
+            calls.append(t.numel())
+            return real(t, *a, **k)
+
+        dist.all_reduce = counting
+        try:
+            for mode, want_calls in (("deferred", [100]), ("inline", [40, 30, 30])):
+                flat = torch.from_numpy(g_all[rank, :100].copy())
+                red = dp.OverlappedGradReducer(mode=mode)
+                calls.clear()
+                for lo_, hi_ in ((60, 100), (30, 60), (0, 30)):
+                    red(flat[lo_:hi_])
+                if mode == "deferred":
+                    assert calls == []                              # nothing moves before wait()
+                red.wait()
+                assert calls == want_calls, (mode, calls)
+                assert np.allclose(flat.numpy(), g_all[:, :100].sum(0), atol=1e-6)
+                red.wait()                                          # idempotent: nothing pending
+                assert calls == want_calls
+        finally:
+            dist.all_reduce = real
         q.put((rank, "ok"))
     except Exception as e:                                           # pragma: no cover
         q.put((rank, repr(e)))
