@@ -343,10 +343,6 @@ gemm2_tcgen05_kernel(const GemmParams p,
                 const bf16* gurow = p.sw_gu + (size_t)(m_ok ? m : 0) * p.sw_ld;
 #pragma unroll 1
                 for (int s = 0; s < G2_BN / 64; ++s) {
-                    unsigned long long kw = ~0ull;
-                    if constexpr (LORA) {
-                        if (m_ok) kw = __ldg(p.lr_bits[0] + (size_t)((n0 >> 6) + s) * p.M + m);
-                    }
                     if (issuer) tma_store_wait_read<0>();
                     asm volatile("bar.sync 1, 128;" ::: "memory");
 #pragma unroll
@@ -546,17 +542,10 @@ gemm2_tcgen05_kernel(const GemmParams p,
                 }
                 continue;
             }
+            if constexpr (!LORA)                              // plain epilogue (alpha, bias, activation, residual)
 #pragma unroll 1
             for (int sl = 0; sl < G2_BN / 128; ++sl) {
                 const int s = wg * (G2_BN / 128) + sl;        // 64-column chunk index inside the tile
-                unsigned long long kw[LORA ? 3 : 1];
-                if constexpr (LORA) {
-#pragma unroll
-                    for (int a = 0; a < 3; ++a) {
-                        kw[a] = ~0ull;
-                        if (a < p.lr_na && m_ok) kw[a] = __ldg(p.lr_bits[a] + (size_t)((n0 >> 6) + s) * p.M + m);
-                    }
-                }
                 if (issuer) tma_store_wait_read<0>();
                 asm volatile("bar.sync %0, 128;" :: "r"(1 + wg) : "memory");
 #pragma unroll
@@ -567,8 +556,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
                     // bias / residual for these 32 columns are requested BEFORE the TMEM wait: issued inside the per-chunk loop
                     // each load sat behind the previous chunk's math and exposed a full memory latency
                     uint4 bv[4], rv[4];
-                    // the dX GEMMs that carry the masked adapter term have no bias / residual: compiled out to keep registers
-                    const bool has_bias = !LORA && p.bias != nullptr, has_res = !LORA && p.residual != nullptr && m_ok;
+                    const bool has_bias = p.bias != nullptr, has_res = p.residual != nullptr && m_ok;
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         const int nn = n + c * 8;
@@ -583,15 +571,6 @@ gemm2_tcgen05_kernel(const GemmParams p,
                         float v[8];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c * 8 + j]) * p.alpha;
-                        if constexpr (LORA) {
-#pragma unroll
-                            for (int a = 0; a < 3; ++a)
-                                if (a < p.lr_na) {      // (not reached: the LORA instantiations leave through the rolled loop above)
-                                    lora_rank16_add8(v, tf[a], la + a * LA_AD_BYTES + (sl * 64 + h * 32 + c * 8 + (lane >> 2)) * LA_REC_BYTES + (lane & 3) * 8,
-                                                     xb + xsel, lane, (unsigned int)(kw[a] >> (h * 32 + c * 8)) & 0xFFu, p.lr_scale);
-                                    xsel ^= 512u;
-                                }
-                        }
                         if (has_bias) {
                             float b[8]; unpack8(bv[c], b);
 #pragma unroll
