@@ -37,41 +37,56 @@ __device__ __forceinline__ void unpack_row(const uint4 (&raw)[HV], int nchunk, f
 }
 
 // z holds the row on entry: RMSNorm (bf16 rounding as MistralRMSNorm) -> z, then LN1 statistics over z.
+// The arithmetic below is written on pairs (FFMA2 / FMUL2 / FADD2 and one packed convert per pair, sm_100): with three bf16 rounding
+// points per element these row kernels are bound by instruction issue (ncu: 946 instructions per warp and row in the scalar form, 30 per
+// element, issue slots 44 % busy at 3 warps per scheduler), not by HBM.
+__device__ __forceinline__ float2 round_bf16_pair(float2 v) {          // float(bf16(v)) for both lanes: one F2FP + two shifts
+    const uint32_t u = pack_bf16(v.x, v.y);
+    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xFFFF0000u));
+}
+__device__ __forceinline__ float2 unpack_pair(uint32_t u) { return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xFFFF0000u)); }
+
 __device__ __forceinline__ RowStats row_norms_z(float (&z)[HV][8], const bf16* __restrict__ wn, int H,
                                                 float eps_rms, float eps_ln, float* red) {
     const int nchunk = H / 8;
-    float ss = 0.f;
+    float2 ss2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < HV; ++i) {
-        const int c = threadIdx.x + i * HT;
-        if (c < nchunk) {
+        if (threadIdx.x + i * HT < nchunk) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) ss += z[i][j] * z[i][j];
+            for (int j = 0; j < 8; j += 2) { const float2 v = make_float2(z[i][j], z[i][j + 1]); ss2 = __ffma2_rn(v, v, ss2); }
         }
     }
     RowStats st;
-    st.rstd_rms = rsqrtf(block_sum(ss, red) / (float)H + eps_rms);
-    float s = 0.f;
+    st.rstd_rms = rsqrtf(block_sum(ss2.x + ss2.y, red) / (float)H + eps_rms);
+    const float2 r2 = make_float2(st.rstd_rms, st.rstd_rms);
+    float2 s2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < HV; ++i) {
         const int c = threadIdx.x + i * HT;
         if (c < nchunk) {
-            float w[8]; load8(wn + c * 8, w);
+            const uint4 wv = __ldg(reinterpret_cast<const uint4*>(wn) + c);
+            const uint32_t wu[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { z[i][j] = bf2f(f2bf(w[j] * bf2f(f2bf(z[i][j] * st.rstd_rms)))); s += z[i][j]; }
+            for (int j = 0; j < 8; j += 2) {
+                const float2 t = round_bf16_pair(__fmul2_rn(make_float2(z[i][j], z[i][j + 1]), r2));      // bf16(x * rstd)
+                const float2 y = round_bf16_pair(__fmul2_rn(unpack_pair(wu[j >> 1]), t));                 // bf16(w * .)
+                z[i][j] = y.x; z[i][j + 1] = y.y;
+                s2 = __fadd2_rn(s2, y);
+            }
         }
     }
-    st.mean1 = block_sum(s, red) / (float)H;
-    float sq = 0.f;
+    st.mean1 = block_sum(s2.x + s2.y, red) / (float)H;
+    const float2 nm2 = make_float2(-st.mean1, -st.mean1);
+    float2 sq2 = make_float2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < HV; ++i) {
-        const int c = threadIdx.x + i * HT;
-        if (c < nchunk) {
+        if (threadIdx.x + i * HT < nchunk) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { const float d = z[i][j] - st.mean1; sq += d * d; }
+            for (int j = 0; j < 8; j += 2) { const float2 d = __fadd2_rn(make_float2(z[i][j], z[i][j + 1]), nm2); sq2 = __ffma2_rn(d, d, sq2); }
         }
     }
-    st.rstd1 = rsqrtf(block_sum(sq, red) / (float)H + eps_ln);
+    st.rstd1 = rsqrtf(block_sum(sq2.x + sq2.y, red) / (float)H + eps_ln);
     return st;
 }
 
@@ -118,15 +133,20 @@ __global__ void __launch_bounds__(HT) hrf_pool_fwd_kernel(const bf16* __restrict
             r = next_live(wsm, r + 1, n);
             if (r < n) load_row_raw(xb + (size_t)r * H, nchunk, raw);                  // in flight during the reductions below
             const RowStats st = row_norms_z(z, wn, H, eps_rms, eps_ln, red);
+            const float2 nm2 = make_float2(-st.mean1, -st.mean1), rs2 = make_float2(st.rstd1, st.rstd1), w2 = make_float2(wgt, wgt);
 #pragma unroll
             for (int i = 0; i < HV; ++i) {
                 const int c = threadIdx.x + i * HT;
                 if (c < nchunk) {
-                    float g[8], bb[8];
-                    load8(g1 + c * 8, g); load8(b1 + c * 8, bb);
+                    const uint4 gv = __ldg(reinterpret_cast<const uint4*>(g1) + c), bv = __ldg(reinterpret_cast<const uint4*>(b1) + c);
+                    const uint32_t gu[4] = {gv.x, gv.y, gv.z, gv.w}, bu[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        acc[i][j] += wgt * bf2f(f2bf((z[i][j] - st.mean1) * st.rstd1 * g[j] + bb[j]));
+                    for (int j = 0; j < 8; j += 2) {
+                        const float2 h = __fmul2_rn(__fadd2_rn(make_float2(z[i][j], z[i][j + 1]), nm2), rs2);         // (z - mean) * rstd
+                        const float2 y = round_bf16_pair(__ffma2_rn(h, unpack_pair(gu[j >> 1]), unpack_pair(bu[j >> 1])));
+                        const float2 a2 = __ffma2_rn(w2, y, make_float2(acc[i][j], acc[i][j + 1]));
+                        acc[i][j] = a2.x; acc[i][j + 1] = a2.y;
+                    }
                 }
             }
         }
@@ -360,54 +380,67 @@ __global__ void __launch_bounds__(HT) hrf_pool_bwd_kernel(const bf16* __restrict
         float z[HV][8];
         const RowStats st = row_norms(xr, wn, H, eps_rms, eps_ln, z, red);
         // LN1 backward
-        float m1 = 0.f, m2 = 0.f;
+        float2 m1p = make_float2(0.f, 0.f), m2p = make_float2(0.f, 0.f);
+        const float2 nm2 = make_float2(-st.mean1, -st.mean1), rs2 = make_float2(st.rstd1, st.rstd1), w2 = make_float2(wgt, wgt);
         float gz[HV][8];
 #pragma unroll
         for (int i = 0; i < HV; ++i) {
             const int c = threadIdx.x + i * HT;
             if (c < nchunk) {
-                float gw[8]; load8(g1 + c * 8, gw);
+                const uint4 gv = __ldg(reinterpret_cast<const uint4*>(g1) + c);
+                const uint32_t gwu[4] = {gv.x, gv.y, gv.z, gv.w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float gu = wgt * dp[i][j];
-                    const float uh = (z[i][j] - st.mean1) * st.rstd1;
-                    ag[i][j] += gu * uh; ab[i][j] += gu;
-                    gz[i][j] = gu * gw[j];
-                    z[i][j] = uh;
-                    m1 += gz[i][j]; m2 += gz[i][j] * uh;
+                for (int j = 0; j < 8; j += 2) {                 // pairs: FMUL2 / FFMA2 / FADD2
+                    const float2 gu = __fmul2_rn(w2, make_float2(dp[i][j], dp[i][j + 1]));
+                    const float2 uh = __fmul2_rn(__fadd2_rn(make_float2(z[i][j], z[i][j + 1]), nm2), rs2);
+                    const float2 a2 = __ffma2_rn(gu, uh, make_float2(ag[i][j], ag[i][j + 1]));
+                    const float2 b2 = __fadd2_rn(make_float2(ab[i][j], ab[i][j + 1]), gu);
+                    const float2 g2 = __fmul2_rn(gu, unpack_pair(gwu[j >> 1]));
+                    ag[i][j] = a2.x; ag[i][j + 1] = a2.y; ab[i][j] = b2.x; ab[i][j + 1] = b2.y;
+                    gz[i][j] = g2.x; gz[i][j + 1] = g2.y;
+                    z[i][j] = uh.x; z[i][j + 1] = uh.y;
+                    m1p = __fadd2_rn(m1p, g2); m2p = __ffma2_rn(g2, uh, m2p);
                 }
             }
         }
         if (dx == nullptr) continue;          // frozen backbone: only the LN1 gradients are needed
-        m1 = block_sum(m1, red) / (float)H;
-        m2 = block_sum(m2, red) / (float)H;
+        const float m1 = block_sum(m1p.x + m1p.y, red) / (float)H;
+        const float m2 = block_sum(m2p.x + m2p.y, red) / (float)H;
         // RMSNorm backward: y = wn * (x * rstd); g = gz * wn; dx = rstd * (g - xh * mean(g * xh))
-        float dot = 0.f;
+        float2 dotp = make_float2(0.f, 0.f);
+        const float2 nm1 = make_float2(-m1, -m1), nm2b = make_float2(-m2, -m2), rr2 = make_float2(st.rstd_rms, st.rstd_rms);
         float xh[HV][8];
 #pragma unroll
         for (int i = 0; i < HV; ++i) {
             const int c = threadIdx.x + i * HT;
             if (c < nchunk) {
-                float w[8];
-                load8(wn + c * 8, w);
-                load8(xr + c * 8, xh[i]);
+                const uint4 wv = __ldg(reinterpret_cast<const uint4*>(wn) + c), xv = __ldg(reinterpret_cast<const uint4*>(xr) + c);
+                const uint32_t wu[4] = {wv.x, wv.y, wv.z, wv.w}, xu[4] = {xv.x, xv.y, xv.z, xv.w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    gz[i][j] = st.rstd1 * (gz[i][j] - m1 - z[i][j] * m2) * w[j];
-                    xh[i][j] *= st.rstd_rms;
-                    dot += gz[i][j] * xh[i][j];
+                for (int j = 0; j < 8; j += 2) {
+                    // gz = rstd1 * (gz - m1 - uh * m2) * w ; xh = x * rstd_rms ; dot += gz * xh
+                    const float2 t = __ffma2_rn(make_float2(z[i][j], z[i][j + 1]), nm2b, __fadd2_rn(make_float2(gz[i][j], gz[i][j + 1]), nm1));
+                    const float2 g2 = __fmul2_rn(__fmul2_rn(rs2, t), unpack_pair(wu[j >> 1]));
+                    const float2 xh2 = __fmul2_rn(unpack_pair(xu[j >> 1]), rr2);
+                    gz[i][j] = g2.x; gz[i][j + 1] = g2.y; xh[i][j] = xh2.x; xh[i][j + 1] = xh2.y;
+                    dotp = __ffma2_rn(g2, xh2, dotp);
                 }
             }
         }
-        dot = block_sum(dot, red) / (float)H;
+        const float dot = block_sum(dotp.x + dotp.y, red) / (float)H;
+        const float2 nd2 = make_float2(-dot, -dot);
 #pragma unroll
         for (int i = 0; i < HV; ++i) {
             const int c = threadIdx.x + i * HT;
             if (c < nchunk) {
-                float o[8];
+                uint4 o;
+                uint32_t* ou = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] = st.rstd_rms * (gz[i][j] - xh[i][j] * dot);
-                store8(dxr + c * 8, o);
+                for (int j = 0; j < 8; j += 2) {
+                    const float2 v = __fmul2_rn(rr2, __ffma2_rn(make_float2(xh[i][j], xh[i][j + 1]), nd2, make_float2(gz[i][j], gz[i][j + 1])));
+                    ou[j >> 1] = pack_bf16(v.x, v.y);
+                }
+                *reinterpret_cast<uint4*>(dxr + c * 8) = o;
             }
         }
     }
