@@ -141,11 +141,14 @@ gemm2_tcgen05_kernel(const GemmParams p,
         // ------------------------------------------------------------------ TMA producer (both CTAs)
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int t = pair; t < num_tiles; t += num_pairs) {
-                int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb);
+            int it = 0;
+            for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+                int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb, p.serp);
                 const int m0 = mb * (2 * BM) + (int)rank * BM;
                 const int n0 = SWIGLU == 1 ? nb * G2_HALF_N + (int)rank * p.swiglu_I : nb * G2_BN + (int)rank * G2_HALF_N;
-                for (int kb = 0; kb < nk; ++kb) {
+                const bool rev = p.serp && (it & 1);              // every CTA of a wave agrees on `it`, so a wave still walks K in step
+                for (int kq = 0; kq < nk; ++kq) {
+                    const int kb = rev ? nk - 1 - kq : kq;        // the MMA issuer consumes ring stages in order, whatever k they hold
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * G2_STAGE_BYTES);
                     const bool second = kb >= p.nk1;
@@ -205,7 +208,7 @@ gemm2_tcgen05_kernel(const GemmParams p,
         int it = 0;
         const bool issuer = (q == 0 && lane == 0);          // one TMA-store issuer per warpgroup
         for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
-            int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb);
+            int mb, nb; tile_coords(t, p.mt, p.nt, p.group_m, mb, nb, p.serp);
             const int m0 = mb * (2 * BM) + (int)rank * BM, n0 = nb * G2_BN;
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;

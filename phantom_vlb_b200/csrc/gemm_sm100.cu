@@ -60,6 +60,8 @@ struct GemmParams {
     int swiglu_I;           // pair kernel, SWIGLU variants: intermediate size I
     const bf16* sw_gu; int sw_ld;   // SWIGLU == 2: saved gate/up activations [M, 2I]
     int stages_used;        // pair kernel: ring depth actually used (<= G2_STAGES), tuning experiments
+    int serp;               // pair kernel, long K: odd M-groups sweep the N-blocks backwards and every second tile of a CTA walks K
+                            // backwards, so that a wave starts on the panels (and at the K end) the previous wave left in L2
     int group_m;            // M-blocks swept together before moving to the next N-block (L2 residency of the A panel)
     // pair kernel, LORA_EPI variants (dX under LoRA dropout): out[m, n] += lr_scale * sum_a keep_a[m, n] * (t_a[m, :] . A_a[:, n]),
     // t [M, 16 lr_na] bf16, A [16 lr_na, N] bf16, keep bits as 64-bit words [N / 64][M] per adapter (lora_dropout.cu)
@@ -69,7 +71,7 @@ struct GemmParams {
     const bf16* rope_cos; const bf16* rope_sin; int rope_S; int rope_ncols;
 };
 
-__device__ __forceinline__ void tile_coords(int t, int mt, int nt, int GROUP_M, int& mb, int& nb) {
+__device__ __forceinline__ void tile_coords(int t, int mt, int nt, int GROUP_M, int& mb, int& nb, int snake = 0) {
     const int per_group = GROUP_M * nt;
     const int g = t / per_group;
     const int first_m = g * GROUP_M;
@@ -77,6 +79,7 @@ __device__ __forceinline__ void tile_coords(int t, int mt, int nt, int GROUP_M, 
     const int r = t - g * per_group;
     mb = first_m + (r % gm);
     nb = r / gm;
+    if (snake && (g & 1)) nb = nt - 1 - nb;      // boustrophedon over N: the next group starts on the B panels this one ended with
 }
 
 // work item t -> (output tile, k-block range) when the contraction is split `splits` ways
@@ -536,7 +539,7 @@ static int launch_gemm(const GemmArgs& a, cudaStream_t stream) {
     p.ad_ld = a.ad_ld; p.ad_lr = a.ad_lr; p.ad_b1 = a.ad_b1; p.ad_b2 = a.ad_b2; p.ad_eps = a.ad_eps; p.ad_wd = a.ad_wd;
     p.ad_bc1 = a.ad_bc1; p.ad_bc2 = a.ad_bc2; p.ad_max_norm = a.ad_max_norm; p.ad_gscale = a.ad_gscale;
     p.ad_two_lambda = a.ad_two_lambda;
-    p.stages_used = 0; p.swiglu_I = 0; p.sw_gu = nullptr; p.sw_ld = 0;
+    p.stages_used = 0; p.serp = 0; p.swiglu_I = 0; p.sw_gu = nullptr; p.sw_ld = 0;
     p.group_m = 8;
     { const char* g = getenv("VLB_GEMM_GROUP_M"); if (g && atoi(g) > 0) p.group_m = atoi(g); }
     // split-K: gradient GEMMs contract over all tokens into a tiny [r, N] output; without it only mt*nt (< 148) CTAs
@@ -606,6 +609,7 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     // algorithmic bytes: a wave of 74 256x256 tiles touches ~17 distinct 256-row panels of K columns each, and the panels of
     // consecutive waves (8 x 7-15 MB of A, all of B) no longer fit the 126 MB L2 at these K.
     p.stages_used = a.K1 >= 8192 ? 4 : G2_STAGES;
+    p.serp = (a.K1 >= 8192 && !getenv("VLB_GEMM_NO_SERP")) ? 1 : 0;
     if (SWIGLU == 1 || SWIGLU == 3) p.stages_used = G2_STAGES - 1;      // the last ring stage is epilogue staging (third buffer / second warpgroup's pair)
     p.rope_cos = reinterpret_cast<const bf16*>(a.rope_cos); p.rope_sin = reinterpret_cast<const bf16*>(a.rope_sin); p.rope_S = a.rope_S; p.rope_ncols = a.rope_ncols;
     p.lr_t = reinterpret_cast<const bf16*>(a.lr_t); p.lr_ldt = a.lr_ldt; p.lr_A = reinterpret_cast<const bf16*>(a.lr_A); p.lr_lda = a.lr_lda;

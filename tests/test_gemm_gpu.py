@@ -115,7 +115,8 @@ def test_gemm_split_k_needs_accumulate():
 
 
 @pytest.mark.parametrize("b_mn", [False, True])
-@pytest.mark.parametrize("M,N,K,R", [(4096, 4096, 512, 0), (4096 + 200, 5120, 320, 48), (16384, 2304, 192, 16), (2560, 8192, 1088, 32)])
+@pytest.mark.parametrize("M,N,K,R", [(4096, 4096, 512, 0), (4096 + 200, 5120, 320, 48), (16384, 2304, 192, 16), (2560, 8192, 1088, 32),
+                                     (2560 + 72, 4096, 8192 + 136, 16)])      # K >= 8192: serpentine tile / K order, three tiles per CTA
 def test_gemm_cta_pair_kernel(M, N, K, R, b_mn):
     """Shapes with >= 74 tiles of 256 x 256 take the cta_group::2 kernel (gemm2_kernel.cuh): ragged M (the peer CTA's rows
     partly / fully out of range), fused LoRA k-block (K2 < 64: zero-filled by TMA), bias + activation + residual epilogue."""
