@@ -608,7 +608,8 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     // 3-deep ring moves the same bytes as 4 but starves the tensor pipe (71 % active). 2.23 / 4.47 GB is 3.1-3.4x the
     // algorithmic bytes: a wave of 74 256x256 tiles touches ~17 distinct 256-row panels of K columns each, and the panels of
     // consecutive waves (8 x 7-15 MB of A, all of B) no longer fit the 126 MB L2 at these K.
-    p.stages_used = a.K1 >= 8192 ? 4 : G2_STAGES;
+    // with the serpentine order (below) K = 14336 is 4 % faster again with 5 stages than with 4 (profiles/r02ba_stages_serp.log)
+    p.stages_used = a.K1 >= 20480 ? 4 : a.K1 >= 8192 ? 5 : G2_STAGES;
     p.serp = (a.K1 >= 8192 && !getenv("VLB_GEMM_NO_SERP")) ? 1 : 0;
     if (SWIGLU == 1 || SWIGLU == 3) p.stages_used = G2_STAGES - 1;      // the last ring stage is epilogue staging (third buffer / second warpgroup's pair)
     p.rope_cos = reinterpret_cast<const bf16*>(a.rope_cos); p.rope_sin = reinterpret_cast<const bf16*>(a.rope_sin); p.rope_S = a.rope_S; p.rope_ncols = a.rope_ncols;
