@@ -600,7 +600,7 @@ static int launch_gemm2(const GemmArgs& a, cudaStream_t stream, void* act = null
     p.ad_p = nullptr; p.ad_m = nullptr; p.ad_v = nullptr; p.ad_pb = nullptr; p.ad_sumsq = nullptr; p.ad_ld = 0;
     // M-blocks (256 rows) swept together before moving to the next N-block: the A panel (group x 256 x K) stays in L2
     // while B streams past it. Measured sustained at M=16384: K=4096 shapes +1.5..3 % at 16, K >= 14336 shapes best at 8.
-    p.group_m = a.K1 <= 8192 ? 16 : 8;
+    p.group_m = a.K1 <= 8192 ? 16 : 8;       // 32 for the 28672-wide gate/up projection looked 2 % better standalone and was 1 % worse in the step
     { const char* g = getenv("VLB_GEMM_GROUP_M"); if (g && atoi(g) > 0) p.group_m = atoi(g); }
     // ring depth: 6 keeps the tensor pipe 95-99 % busy, but the deeper the ring the further the CTAs of a wave drift apart along K
     // and the less they share each other's A / B panels in L2. ncu at M = 16384 (profiles/r02r_ring_depth.md): K = 14336 reads
